@@ -1,0 +1,1034 @@
+// gpu_ec.cu — libgpu_ec.so: context, launch logic and the extern "C" entry points declared in
+// include/gpu_ec.h. The data path runs only in the CUDA kernels of rs_kernels.cuh and
+// crc_kernels.cuh; there is no CPU fallback (no device -> GPU_EC_ERR_NO_DEVICE).
+#include "../../include/gpu_ec.h"
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "crc_kernels.cuh"
+#include "host_math.hpp"
+#include "rs_kernels.cuh"
+
+namespace gpu_ec {
+
+static thread_local std::string t_last_error;
+static std::atomic<uint64_t> g_launches{0};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            char buf_[512];                                                                        \
+            snprintf(buf_, sizeof buf_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            t_last_error = buf_;                                                                   \
+            return (e_ == cudaErrorMemoryAllocation) ? GPU_EC_ERR_OOM : GPU_EC_ERR_CUDA;           \
+        }                                                                                          \
+    } while (0)
+#define RET(call)                   \
+    do {                            \
+        int rc_ = (call);           \
+        if (rc_ != GPU_EC_OK) return rc_; \
+    } while (0)
+
+static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------------------------------------
+constexpr int NSLOT = 4;
+struct Slot {
+    cudaStream_t stream = nullptr;
+    uint8_t *dbuf = nullptr;
+    size_t cap = 0;
+    bool busy = false;
+};
+struct Dev {
+    int ordinal = -1;
+    bool ready = false;
+    int sm_count = 0;
+    std::mutex mu;
+    std::condition_variable cv;
+    Slot slots[NSLOT];
+};
+struct Ctx {
+    std::mutex mu;
+    bool inited = false;
+    int status = GPU_EC_OK;
+    std::vector<std::unique_ptr<Dev>> devs;
+    std::vector<int> active;
+    std::atomic<uint64_t> rr{0};
+};
+static Ctx &ctx() { static Ctx c; return c; }
+
+template <int K>
+static int set_lut8_attr() {
+    CK(cudaFuncSetAttribute(rs_lut8_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 256 * 32 * 4));
+    return GPU_EC_OK;
+}
+
+static int dev_prepare(Dev &d) {
+    std::lock_guard<std::mutex> lk(d.mu);
+    if (d.ready) return GPU_EC_OK;
+    CK(cudaSetDevice(d.ordinal));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, d.ordinal));
+    if (prop.major < 10) {
+        t_last_error = "gpu_ec needs an sm_100a (B200) device";
+        return GPU_EC_ERR_NO_DEVICE;
+    }
+    d.sm_count = prop.multiProcessorCount;
+    static uint32_t tabs[2][4][256];
+    static std::once_flag once;
+    std::call_once(once, [] { for (int p = 0; p < 2; p++) crc_tables(kPolyReflected[p], tabs[p]); });
+    CK(cudaMemcpyToSymbol(g_crc_tab, tabs, sizeof tabs));
+    RET(set_lut8_attr<1>()); RET(set_lut8_attr<2>()); RET(set_lut8_attr<3>()); RET(set_lut8_attr<4>());
+    RET(set_lut8_attr<5>()); RET(set_lut8_attr<6>()); RET(set_lut8_attr<7>());
+    CK(cudaFuncSetAttribute(rs_lut4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_LUT4_MAX_IN * 4096));
+    CK(cudaFuncSetAttribute(crc_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+    for (auto &s : d.slots) CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    // keep stream-ordered scratch cached instead of returning it to the OS after every call
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, d.ordinal) == cudaSuccess) {
+        unsigned long long thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    d.ready = true;
+    return GPU_EC_OK;
+}
+
+static int ensure_init() {
+    Ctx &c = ctx();
+    std::lock_guard<std::mutex> lk(c.mu);
+    if (c.inited) return c.status;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        t_last_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        return GPU_EC_ERR_NO_DEVICE;  // not latched: a later call may find a device
+    }
+    for (int i = 0; i < n; i++) {
+        c.devs.emplace_back(new Dev());
+        c.devs.back()->ordinal = i;
+    }
+    if (c.active.empty()) for (int i = 0; i < n; i++) c.active.push_back(i);
+    c.inited = true;
+    c.status = GPU_EC_OK;
+    return GPU_EC_OK;
+}
+
+static int get_dev(int ordinal, Dev **out) {
+    RET(ensure_init());
+    Ctx &c = ctx();
+    if (ordinal < 0 || ordinal >= static_cast<int>(c.devs.size())) return GPU_EC_ERR_INVALID_ARG;
+    Dev &d = *c.devs[ordinal];
+    RET(dev_prepare(d));
+    *out = &d;
+    return GPU_EC_OK;
+}
+
+// device that owns a device pointer (for the _dev entry points)
+static int dev_of_ptr(const void *p, Dev **out) {
+    RET(ensure_init());
+    cudaPointerAttributes a;
+    CK(cudaPointerGetAttributes(&a, p));
+    if (a.type != cudaMemoryTypeDevice && a.type != cudaMemoryTypeManaged) {
+        t_last_error = "pointer is not device memory";
+        return GPU_EC_ERR_INVALID_ARG;
+    }
+    RET(get_dev(a.device, out));
+    CK(cudaSetDevice(a.device));
+    return GPU_EC_OK;
+}
+
+struct Lease {
+    Dev *d = nullptr;
+    Slot *s = nullptr;
+    ~Lease() { release(); }
+    void release() {
+        if (d && s) {
+            std::lock_guard<std::mutex> lk(d->mu);
+            s->busy = false;
+            d->cv.notify_one();
+        }
+        d = nullptr; s = nullptr;
+    }
+};
+
+static int lease_on(Dev &d, Lease &l) {
+    {
+        std::unique_lock<std::mutex> lk(d.mu);
+        Slot *s = nullptr;
+        d.cv.wait(lk, [&] {
+            for (auto &x : d.slots) if (!x.busy) { s = &x; return true; }
+            return false;
+        });
+        s->busy = true;
+        l.d = &d; l.s = s;
+    }
+    CK(cudaSetDevice(d.ordinal));
+    return GPU_EC_OK;
+}
+
+static int lease_any(Lease &l) {
+    RET(ensure_init());
+    Ctx &c = ctx();
+    int ord;
+    {
+        std::lock_guard<std::mutex> lk(c.mu);
+        ord = c.active[c.rr.fetch_add(1) % c.active.size()];
+    }
+    Dev *d;
+    RET(get_dev(ord, &d));
+    return lease_on(*d, l);
+}
+
+static int slot_reserve(Slot &s, size_t bytes) {
+    if (s.cap >= bytes) return GPU_EC_OK;
+    if (s.dbuf) { CK(cudaStreamSynchronize(s.stream)); CK(cudaFree(s.dbuf)); s.dbuf = nullptr; s.cap = 0; }
+    size_t want = round_up(bytes + bytes / 8, 1 << 20);
+    CK(cudaMalloc(&s.dbuf, want));
+    CK(cudaMemsetAsync(s.dbuf, 0, want, s.stream));
+    s.cap = want;
+    return GPU_EC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// launch logic
+
+static int check_stripes(const gpu_ec_stripes *s) {
+    if (!s || !s->base) return GPU_EC_ERR_INVALID_ARG;
+    if ((reinterpret_cast<uintptr_t>(s->base) & 15) || (s->shard_stride & 15) || (s->stripe_stride & 15)) return GPU_EC_ERR_UNALIGNED;
+    if (s->shard_stride < round_up(s->shard_len, 16)) return GPU_EC_ERR_INVALID_ARG;
+    return GPU_EC_OK;
+}
+
+template <int K>
+static void launch_lut8(const RsParams &p, int grid, cudaStream_t st) {
+    rs_lut8_kernel<K><<<grid, RS_THREADS, K * 256 * 32 * 4, st>>>(p);
+}
+
+// out slot out_idx[r] = XOR_j rows[r*n_in+j] * in slot in_idx[j]
+static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, const int *in_idx, int n_in,
+                        const int *out_idx, int n_out, cudaStream_t st) {
+    if (n_in <= 0 || n_out <= 0) return GPU_EC_ERR_INVALID_ARG;
+    if (s.n_stripes == 0 || s.shard_len == 0) return GPU_EC_OK;
+    RsParams p;
+    memset(&p, 0, sizeof p);
+    p.base = s.base;
+    p.shard_stride = s.shard_stride;
+    p.stripe_stride = s.stripe_stride;
+    p.nvec = static_cast<unsigned int>(div_up(s.shard_len, 16));
+    p.tiles_per_stripe = static_cast<unsigned int>(div_up(p.nvec, RS_THREADS));
+    p.n_tiles = static_cast<unsigned long long>(s.n_stripes) * p.tiles_per_stripe;
+    const int grid = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count)));
+    for (int o0 = 0; o0 < n_out; o0 += RS_MAX_OUT) {
+        const int no = std::min(RS_MAX_OUT, n_out - o0);
+        p.n_out = no;
+        for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[o0 + r];
+        const int max_in = (n_in <= RS_LUT8_MAX_IN) ? RS_LUT8_MAX_IN : RS_LUT4_MAX_IN;
+        for (int j0 = 0; j0 < n_in; j0 += max_in) {
+            const int ni = std::min(max_in, n_in - j0);
+            p.n_in = ni;
+            p.accumulate = j0 > 0;
+            for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j0 + j];
+            for (int r = 0; r < no; r++)
+                for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(o0 + r) * n_in + j0 + j];
+            if (n_in <= RS_LUT8_MAX_IN) {
+                switch (ni) {
+                    case 1: launch_lut8<1>(p, grid, st); break;
+                    case 2: launch_lut8<2>(p, grid, st); break;
+                    case 3: launch_lut8<3>(p, grid, st); break;
+                    case 4: launch_lut8<4>(p, grid, st); break;
+                    case 5: launch_lut8<5>(p, grid, st); break;
+                    case 6: launch_lut8<6>(p, grid, st); break;
+                    default: launch_lut8<7>(p, grid, st); break;
+                }
+            } else {
+                rs_lut4_kernel<<<grid, RS_THREADS, ni * 4096, st>>>(p);
+            }
+            g_launches++;
+            CK(cudaGetLastError());
+        }
+    }
+    return GPU_EC_OK;
+}
+
+struct CrcJob {
+    const uint8_t *base = nullptr;
+    size_t n_buf = 0, buf_stride = 0, len = 0;
+    size_t chunk = 0;          // 0 = whole-buffer mode (one CRC per buffer)
+    int poly = 0;
+    uint32_t *out = nullptr;   // may be null in verify mode
+    size_t out_stride = 0;
+    int big_endian = 0;
+    const uint8_t *expect_be = nullptr;
+    unsigned long long *first_bad = nullptr;
+};
+
+static int launch_combine(Dev &d, const uint32_t *partial, size_t n_buf, size_t segs_per_buf, size_t seg_bytes,
+                          size_t len, size_t group, const CrcJob &j, cudaStream_t st) {
+    const uint32_t P = kPolyReflected[j.poly];
+    CombineParams c;
+    memset(&c, 0, sizeof c);
+    c.partial = partial;
+    c.n_buf = n_buf;
+    c.segs_per_buf = segs_per_buf;
+    c.group = static_cast<unsigned int>(group);
+    c.outs_per_buf = div_up(segs_per_buf, group);
+    c.last_cnt = static_cast<unsigned int>(segs_per_buf - (c.outs_per_buf - 1) * group);
+    const size_t rag = len % seg_bytes;
+    c.last_has_rag = rag ? 1 : 0;
+    c.x_rag = x8n_modp(rag, P);
+    c.x1 = x8n_modp(seg_bytes, P);
+    c.poly_bits = P;
+    const unsigned int maxcnt = static_cast<unsigned int>(std::max<size_t>(c.group, c.last_cnt));
+    const unsigned int T = static_cast<unsigned int>(std::min<size_t>(1024, round_up(std::min<unsigned int>(maxcnt, 1024u), 32)));
+    auto plan = [&](unsigned int nreg, unsigned int &R, unsigned int &runs, uint32_t *xr, uint32_t &xl) {
+        if (nreg == 0) { R = 1; runs = 0; xl = 0x80000000u; for (int i = 0; i < COMBINE_MAX_LOG; i++) xr[i] = 0x80000000u; return; }
+        R = static_cast<unsigned int>(div_up(nreg, T));
+        runs = static_cast<unsigned int>(div_up(nreg, R));
+        const unsigned int llast = nreg - (runs - 1) * R;
+        xl = x8n_modp(static_cast<uint64_t>(seg_bytes) * llast, P);
+        uint32_t v = x8n_modp(static_cast<uint64_t>(seg_bytes) * R, P);
+        for (int i = 0; i < COMBINE_MAX_LOG; i++) { xr[i] = v; v = multmodp(v, v, P); }
+    };
+    plan(c.group, c.R_reg, c.runs_reg, c.xr_reg, c.xl_reg);
+    plan(c.last_cnt - (c.last_has_rag ? 1u : 0u), c.R_last, c.runs_last, c.xr_last, c.xl_last);
+    c.out = j.out;
+    c.out_stride = j.out_stride;
+    c.big_endian = j.big_endian;
+    c.expect_be = j.expect_be;
+    c.first_bad = j.first_bad;
+    const unsigned long long total = static_cast<unsigned long long>(n_buf) * c.outs_per_buf;
+    const int per_sm = std::max(1, 2048 / static_cast<int>(T));
+    const int grid = static_cast<int>(std::min<unsigned long long>(total, static_cast<unsigned long long>(d.sm_count) * per_sm));
+    crc_combine_kernel<<<grid, T, 0, st>>>(c);
+    g_launches++;
+    CK(cudaGetLastError());
+    return GPU_EC_OK;
+}
+
+static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
+    if (j.n_buf == 0) return GPU_EC_OK;
+    const bool whole = (j.chunk == 0);
+    if (j.len == 0) {
+        if (whole && j.out) {  // crc32fast of nothing is 0
+            if (j.out_stride == 1) CK(cudaMemsetAsync(j.out, 0, 4 * j.n_buf, st));
+            else CK(cudaMemset2DAsync(j.out, 4 * j.out_stride, 0, 4, j.n_buf, st));
+        }
+        return GPU_EC_OK;
+    }
+    const bool aligned = !(reinterpret_cast<uintptr_t>(j.base) & 15) && !(j.buf_stride & 15) &&
+                         !(j.expect_be && (reinterpret_cast<uintptr_t>(j.expect_be) & 3));
+    const unsigned long long lanes_wave = static_cast<unsigned long long>(d.sm_count) * CRC_THREADS;
+    size_t G = 0;
+    if (aligned) {
+        const unsigned long long total = static_cast<unsigned long long>(j.n_buf) * j.len;
+        if (whole) {
+            G = 512;  // most parallelism; longer segments only when there are waves to spare
+            for (size_t g : {size_t(16384), size_t(8192), size_t(4096), size_t(2048), size_t(1024)})
+                if (total / g >= 4 * lanes_wave) { G = g; break; }
+        } else if (j.chunk % 128 == 0) {
+            if (j.chunk <= 1024) {
+                G = j.chunk;  // one lane per chunk, CRC written directly
+            } else {
+                for (size_t g : {size_t(4096), size_t(2048), size_t(1024), size_t(512)})
+                    if (j.chunk % g == 0 && total / g >= 4 * lanes_wave) { G = g; break; }
+                if (!G)
+                    for (size_t g : {size_t(512), size_t(256), size_t(128)})
+                        if (j.chunk % g == 0) { G = g; break; }
+            }
+        }
+    }
+    if (G == 0) {  // generic fallback kernel (odd chunk size / unaligned): one thread per chunk
+        const size_t chunk = whole ? j.len : j.chunk;
+        CrcSlowParams sp;
+        memset(&sp, 0, sizeof sp);
+        sp.base = j.base; sp.buf_stride = j.buf_stride; sp.n_buf = j.n_buf; sp.len = j.len; sp.chunk = chunk;
+        sp.chunks_per_buf = div_up(j.len, chunk);
+        sp.out = j.out; sp.out_stride = j.out_stride; sp.poly = j.poly; sp.big_endian = j.big_endian;
+        sp.expect_be = j.expect_be; sp.first_bad = j.first_bad;
+        const unsigned long long total = sp.n_buf * sp.chunks_per_buf;
+        const int grid = static_cast<int>(std::min<unsigned long long>(div_up(total, 128), static_cast<unsigned long long>(d.sm_count) * 16));
+        crc_chunks_slow_kernel<<<grid, 128, 0, st>>>(sp);
+        g_launches++;
+        CK(cudaGetLastError());
+        return GPU_EC_OK;
+    }
+    CrcParams p;
+    memset(&p, 0, sizeof p);
+    p.base = j.base; p.buf_stride = j.buf_stride; p.n_buf = j.n_buf; p.len = j.len;
+    p.G = static_cast<unsigned int>(G);
+    p.nfull = j.len / G;
+    p.rag = static_cast<unsigned int>(j.len % G);
+    p.segs_per_buf = p.nfull + (p.rag ? 1 : 0);
+    p.tiles_per_buf = div_up(p.nfull, 32);
+    p.poly = j.poly;
+    const bool direct = !whole && G == j.chunk;
+    uint32_t *scratch = nullptr;
+    if (direct) {
+        p.out = j.out; p.out_stride = j.out_stride; p.big_endian = j.big_endian;
+        p.expect_be = j.expect_be; p.first_bad = j.first_bad;
+    } else {
+        CK(cudaMallocAsync(&scratch, 4ull * j.n_buf * p.segs_per_buf, st));
+        p.out = scratch; p.out_stride = p.segs_per_buf;
+    }
+    const unsigned long long warps = j.n_buf * p.tiles_per_buf + (p.rag ? j.n_buf : 0);
+    const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(d.sm_count))));
+    crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
+    g_launches++;
+    CK(cudaGetLastError());
+    if (!direct) {
+        const size_t group = whole ? p.segs_per_buf : j.chunk / G;
+        int rc = launch_combine(d, scratch, j.n_buf, p.segs_per_buf, G, j.len, group, j, st);
+        CK(cudaFreeAsync(scratch, st));
+        RET(rc);
+    }
+    return GPU_EC_OK;
+}
+
+// CRC of the original buffer from the data-shard CRCs: constants for stripe_full_crc_kernel.
+// The original's `len` bytes cover n_full whole data shards plus (maybe) a `rem`-byte prefix of
+// the next one, whose remaining S-rem bytes are the zero padding of erasure.rs:18.
+static void full_crc_constants(FullCrcParams &f, size_t S, size_t original_len, int poly) {
+    const uint32_t P = kPolyReflected[poly];
+    const size_t rem = original_len % S;
+    const size_t pad = rem ? S - rem : 0;
+    f.n_full = static_cast<int>(original_len / S);
+    f.has_part = rem ? 1 : 0;
+    f.xS = x8n_modp(S, P);
+    f.xLp = x8n_modp(rem, P);
+    // x^-1: undo one "multiply by x" step; then raise to 8*pad
+    const uint32_t xinv = ((0x80000000u ^ P) << 1) | 1u;
+    uint32_t r = 0x80000000u, sq = xinv;
+    for (uint64_t e = 8ull * pad; e; e >>= 1) { if (e & 1) r = multmodp(sq, r, P); sq = multmodp(sq, sq, P); }
+    f.x_inv_pad = r;
+    uint32_t c = 0xFFFFFFFFu;  // CRC of `pad` zero bytes
+    for (size_t i = 0; i < pad; i++) for (int b = 0; b < 8; b++) c = (c >> 1) ^ ((c & 1) ? P : 0);
+    f.crc_zeros_pad = pad ? ~c : 0u;
+    f.poly_bits = P;
+}
+static uint32_t full_crc_host(const uint32_t *shard_crc, size_t S, size_t original_len, int poly) {
+    FullCrcParams f;
+    full_crc_constants(f, S, original_len, poly);
+    uint32_t acc = 0;
+    for (int j = 0; j < f.n_full; j++) acc = multmodp(acc, f.xS, f.poly_bits) ^ shard_crc[j];
+    if (f.has_part) {
+        const uint32_t part = multmodp(shard_crc[f.n_full] ^ f.crc_zeros_pad, f.x_inv_pad, f.poly_bits);
+        acc = multmodp(acc, f.xLp, f.poly_bits) ^ part;
+    }
+    return acc;
+}
+
+static int check_km(int k, int m) {
+    if (k <= 0 || m <= 0) return GPU_EC_ERR_ZERO_SHARDS;
+    if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;
+    return GPU_EC_OK;
+}
+
+static int encode_dev_impl(Dev &d, const gpu_ec_stripes &s, int k, int m, cudaStream_t st) {
+    const Mat &M = coding_matrix(k, m);
+    std::vector<int> in(k), out(m);
+    for (int i = 0; i < k; i++) in[i] = i;
+    for (int i = 0; i < m; i++) out[i] = k + i;
+    return launch_apply(d, s, &M[static_cast<size_t>(k) * k], in.data(), k, out.data(), m, st);
+}
+
+static int reconstruct_plan(int k, int m, const uint8_t *present, DecodePlan &plan, bool &noop) {
+    RET(check_km(k, m));
+    int np = 0;
+    for (int i = 0; i < k + m; i++) np += present[i] ? 1 : 0;
+    noop = (np == k + m);
+    if (noop) return GPU_EC_OK;
+    if (np < k) return GPU_EC_ERR_TOO_FEW_PRESENT;
+    int rc = decode_plan(k, m, present, plan);
+    if (rc == -1) return GPU_EC_ERR_TOO_FEW_PRESENT;
+    if (rc) return GPU_EC_ERR_SINGULAR;
+    return GPU_EC_OK;
+}
+
+}  // namespace gpu_ec
+
+using namespace gpu_ec;
+
+// =============================================================================================
+extern "C" {
+
+int gpu_ec_init(void) {
+    RET(ensure_init());
+    Ctx &c = ctx();
+    std::vector<int> act;
+    { std::lock_guard<std::mutex> lk(c.mu); act = c.active; }
+    for (int o : act) { Dev *d; RET(get_dev(o, &d)); }
+    return GPU_EC_OK;
+}
+
+void gpu_ec_shutdown(void) {
+    Ctx &c = ctx();
+    std::lock_guard<std::mutex> lk(c.mu);
+    for (auto &dp : c.devs) {
+        Dev &d = *dp;
+        std::lock_guard<std::mutex> lk2(d.mu);
+        if (!d.ready) continue;
+        cudaSetDevice(d.ordinal);
+        for (auto &s : d.slots) {
+            if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); s.stream = nullptr; }
+            if (s.dbuf) { cudaFree(s.dbuf); s.dbuf = nullptr; s.cap = 0; }
+        }
+        d.ready = false;
+    }
+}
+
+int gpu_ec_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int gpu_ec_set_devices(const int *devices, int n) {
+    if (!devices || n <= 0) return GPU_EC_ERR_INVALID_ARG;
+    const int have = gpu_ec_device_count();
+    if (have <= 0) return GPU_EC_ERR_NO_DEVICE;
+    for (int i = 0; i < n; i++) if (devices[i] < 0 || devices[i] >= have) return GPU_EC_ERR_INVALID_ARG;
+    Ctx &c = ctx();
+    std::lock_guard<std::mutex> lk(c.mu);
+    c.active.assign(devices, devices + n);
+    return GPU_EC_OK;
+}
+
+const char *gpu_ec_strerror(int status) {
+    switch (status) {
+        case GPU_EC_OK: return "ok";
+        case GPU_EC_ERR_ZERO_SHARDS: return "data_shards and parity_shards must both be > 0";
+        case GPU_EC_ERR_EMPTY_DATA: return "data must not be empty";
+        case GPU_EC_ERR_TOO_MANY_SHARDS: return "RS init error: TooManyShards";
+        case GPU_EC_ERR_TOO_FEW_PRESENT: return "RS reconstruct error: TooFewShardsPresent";
+        case GPU_EC_ERR_EMPTY_SHARD: return "RS reconstruct error: EmptyShard";
+        case GPU_EC_ERR_SHARD_SIZE: return "RS reconstruct error: IncorrectShardSize";
+        case GPU_EC_ERR_COUNT_MISMATCH: return "Checksum count mismatch";
+        case GPU_EC_ERR_CRC_MISMATCH: return "Checksum mismatch at chunk";
+        case GPU_EC_ERR_CUDA: return "CUDA error";
+        case GPU_EC_ERR_OOM: return "out of device memory";
+        case GPU_EC_ERR_INVALID_ARG: return "invalid argument";
+        case GPU_EC_ERR_NO_DEVICE: return "no usable CUDA device (gpu_ec has no CPU fallback)";
+        case GPU_EC_ERR_UNALIGNED: return "device pointer or stride not 16-byte aligned";
+        case GPU_EC_ERR_SINGULAR: return "RS reconstruct error: singular decode matrix";
+        default: return "unknown gpu_ec status";
+    }
+}
+
+const char *gpu_ec_last_error(void) { return t_last_error.c_str(); }
+
+int gpu_ec_alloc_pinned(void **ptr, size_t bytes) {
+    if (!ptr) return GPU_EC_ERR_INVALID_ARG;
+    RET(ensure_init());
+    CK(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocPortable));
+    return GPU_EC_OK;
+}
+int gpu_ec_free_pinned(void *ptr) {
+    if (!ptr) return GPU_EC_OK;
+    CK(cudaFreeHost(ptr));
+    return GPU_EC_OK;
+}
+
+size_t gpu_ec_shard_len(size_t len, size_t k) { return k ? (len + k - 1) / k : 0; }
+
+int gpu_ec_rs_matrix(int k, int m, uint8_t *out) {
+    RET(check_km(k, m));
+    if (!out) return GPU_EC_ERR_INVALID_ARG;
+    const Mat &M = coding_matrix(k, m);
+    memcpy(out, M.data(), M.size());
+    return GPU_EC_OK;
+}
+
+int gpu_ec_rs_decode_matrix(int k, int m, const uint8_t *present, uint8_t *rows_out, int *missing_out,
+                            int *survivors_out, int *n_missing_out) {
+    if (!present || !rows_out || !missing_out || !survivors_out || !n_missing_out) return GPU_EC_ERR_INVALID_ARG;
+    DecodePlan plan;
+    bool noop = false;
+    RET(reconstruct_plan(k, m, present, plan, noop));
+    if (noop) {
+        *n_missing_out = 0;
+        for (int i = 0; i < k; i++) survivors_out[i] = i;
+        return GPU_EC_OK;
+    }
+    *n_missing_out = static_cast<int>(plan.missing.size());
+    memcpy(rows_out, plan.rows.data(), plan.rows.size());
+    for (size_t i = 0; i < plan.missing.size(); i++) missing_out[i] = plan.missing[i];
+    for (int i = 0; i < k; i++) survivors_out[i] = plan.survivors[i];
+    return GPU_EC_OK;
+}
+
+void gpu_ec_meta_encode_be(const uint32_t *crcs, size_t n, uint8_t *out) {
+    for (size_t i = 0; i < n; i++) {
+        out[4 * i + 0] = static_cast<uint8_t>(crcs[i] >> 24);
+        out[4 * i + 1] = static_cast<uint8_t>(crcs[i] >> 16);
+        out[4 * i + 2] = static_cast<uint8_t>(crcs[i] >> 8);
+        out[4 * i + 3] = static_cast<uint8_t>(crcs[i]);
+    }
+}
+
+uint32_t gpu_ec_crc32_combine(uint32_t crc1, uint32_t crc2, size_t len2, int poly) {
+    const uint32_t P = kPolyReflected[poly ? 1 : 0];
+    return multmodp(x8n_modp(len2, P), crc1, P) ^ crc2;
+}
+
+uint64_t gpu_ec_kernel_launch_count(void) { return g_launches.load(); }
+
+// ---------------------------------------------------------------------------------------------
+// device-resident entry points
+
+int gpu_ec_encode_dev(const gpu_ec_stripes *s, int k, int m, void *stream) {
+    RET(check_km(k, m));
+    RET(check_stripes(s));
+    Dev *d;
+    RET(dev_of_ptr(s->base, &d));
+    return encode_dev_impl(*d, *s, k, m, static_cast<cudaStream_t>(stream));
+}
+
+int gpu_ec_reconstruct_dev(const gpu_ec_stripes *s, const uint8_t *present, int k, int m, void *stream) {
+    if (!present) return GPU_EC_ERR_INVALID_ARG;
+    DecodePlan plan;
+    bool noop = false;
+    RET(reconstruct_plan(k, m, present, plan, noop));
+    if (noop) return GPU_EC_OK;
+    RET(check_stripes(s));
+    if (s->shard_len == 0) return GPU_EC_ERR_EMPTY_SHARD;
+    Dev *d;
+    RET(dev_of_ptr(s->base, &d));
+    return launch_apply(*d, *s, plan.rows.data(), plan.survivors.data(), k, plan.missing.data(),
+                        static_cast<int>(plan.missing.size()), static_cast<cudaStream_t>(stream));
+}
+
+int gpu_ec_apply_matrix_dev(const gpu_ec_stripes *s, const uint8_t *rows, const int *in_idx, int n_in,
+                            const int *out_idx, int n_out, void *stream) {
+    if (!rows || !in_idx || !out_idx || n_in <= 0 || n_out <= 0 || n_in > 256 || n_out > 256) return GPU_EC_ERR_INVALID_ARG;
+    RET(check_stripes(s));
+    Dev *d;
+    RET(dev_of_ptr(s->base, &d));
+    return launch_apply(*d, *s, rows, in_idx, n_in, out_idx, n_out, static_cast<cudaStream_t>(stream));
+}
+
+int gpu_ec_crc32_chunks_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, size_t chunk,
+                            int poly, uint32_t *out, size_t out_stride, int big_endian, void *stream) {
+    if (!base || !out || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    Dev *d;
+    RET(dev_of_ptr(base, &d));
+    CrcJob j;
+    j.base = base; j.n_buf = n_buf; j.buf_stride = buf_stride; j.len = len; j.chunk = chunk; j.poly = poly;
+    j.out = out; j.out_stride = out_stride; j.big_endian = big_endian;
+    return launch_crc(*d, j, static_cast<cudaStream_t>(stream));
+}
+
+int gpu_ec_crc32_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, int poly, uint32_t *out,
+                     void *stream) {
+    if (!base || !out || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    Dev *d;
+    RET(dev_of_ptr(base, &d));
+    CrcJob j;
+    j.base = base; j.n_buf = n_buf; j.buf_stride = buf_stride; j.len = len; j.chunk = 0; j.poly = poly;
+    j.out = out; j.out_stride = 1;
+    return launch_crc(*d, j, static_cast<cudaStream_t>(stream));
+}
+
+int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int poly, const uint8_t *meta_be,
+                             long long *first_bad, void *stream) {
+    if (!data || !meta_be || !first_bad || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    Dev *d;
+    RET(dev_of_ptr(data, &d));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(cudaMemsetAsync(first_bad, 0xFF, 8, st));
+    CrcJob j;
+    j.base = data; j.n_buf = 1; j.buf_stride = round_up(len, 16); j.len = len; j.chunk = chunk; j.poly = poly;
+    j.expect_be = meta_be; j.first_bad = reinterpret_cast<unsigned long long *>(first_bad);
+    RET(launch_crc(*d, j, st));
+    first_bad_finish_kernel<<<1, 1, 0, st>>>(reinterpret_cast<unsigned long long *>(first_bad));
+    g_launches++;
+    CK(cudaGetLastError());
+    return GPU_EC_OK;
+}
+
+int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original_len, int poly,
+                          uint32_t *shard_crc, uint32_t *full_crc, void *stream) {
+    RET(check_km(k, m));
+    RET(check_stripes(s));
+    if (!shard_crc || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    const size_t S = s->shard_len;
+    if (original_len == 0) original_len = S * static_cast<size_t>(k);
+    if (S == 0 || original_len > S * static_cast<size_t>(k)) return GPU_EC_ERR_INVALID_ARG;
+    Dev *d;
+    RET(dev_of_ptr(s->base, &d));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int n = k + m;
+    // stripe groups of <= 64 MiB so the parity just written is checksummed while still in L2
+    const size_t per_stripe = static_cast<size_t>(n) * S;
+    const size_t grp = std::max<size_t>(1, (64ull << 20) / std::max<size_t>(per_stripe, 1));
+    for (size_t i0 = 0; i0 < s->n_stripes; i0 += grp) {
+        const size_t cnt = std::min(grp, s->n_stripes - i0);
+        gpu_ec_stripes sub = *s;
+        sub.base = s->base + i0 * s->stripe_stride;
+        sub.n_stripes = cnt;
+        RET(encode_dev_impl(*d, sub, k, m, st));
+        CrcJob j;
+        j.buf_stride = s->shard_stride; j.len = S; j.chunk = 0; j.poly = poly; j.out_stride = 1;
+        if (s->stripe_stride == static_cast<size_t>(n) * s->shard_stride) {  // all shards of the group at one stride
+            j.base = sub.base; j.n_buf = cnt * n; j.out = shard_crc + i0 * n;
+            RET(launch_crc(*d, j, st));
+        } else {
+            for (size_t i = 0; i < cnt; i++) {
+                j.base = sub.base + i * s->stripe_stride; j.n_buf = n; j.out = shard_crc + (i0 + i) * n;
+                RET(launch_crc(*d, j, st));
+            }
+        }
+    }
+    if (full_crc) {
+        FullCrcParams f;
+        memset(&f, 0, sizeof f);
+        full_crc_constants(f, S, original_len, poly);
+        f.shard_crc = shard_crc; f.full_crc = full_crc; f.n_stripes = s->n_stripes; f.n_shards = n;
+        const int grid = static_cast<int>(std::min<size_t>(div_up(s->n_stripes, 128), 1024));
+        stripe_full_crc_kernel<<<grid, 128, 0, st>>>(f);
+        g_launches++;
+        CK(cudaGetLastError());
+    }
+    return GPU_EC_OK;
+}
+
+int gpu_ec_fill_synthetic_dev(uint8_t *out, size_t len, uint64_t seed, uint64_t byte_offset, void *stream) {
+    if (!out) return GPU_EC_ERR_INVALID_ARG;
+    if ((reinterpret_cast<uintptr_t>(out) & 7) || (byte_offset & 7)) return GPU_EC_ERR_UNALIGNED;
+    if (len == 0) return GPU_EC_OK;
+    Dev *d;
+    RET(dev_of_ptr(out, &d));
+    const size_t words = div_up(len, 8);
+    const int grid = static_cast<int>(std::min<size_t>(div_up(words, 256), static_cast<size_t>(d->sm_count) * 16));
+    fill_synthetic_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(out, len, seed, byte_offset);
+    g_launches++;
+    CK(cudaGetLastError());
+    return GPU_EC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-pointer entry points
+
+int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const *shards_out,
+                  uint32_t *shard_crc_out, uint32_t *full_crc_out, uint8_t *const *meta_out) {
+    if (k <= 0 || m <= 0) return GPU_EC_ERR_ZERO_SHARDS;   // erasure.rs:8-10 (checked first there too)
+    if (len == 0) return GPU_EC_ERR_EMPTY_DATA;            // erasure.rs:11-13
+    if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;    // ReedSolomon::new
+    if (!data || !shards_out) return GPU_EC_ERR_INVALID_ARG;
+    const int n = k + m;
+    const size_t S = gpu_ec_shard_len(len, k);
+    const size_t pitch = round_up(S, 256);
+    const size_t n_meta = div_up(S, 512);
+    const size_t crc_off = static_cast<size_t>(n) * pitch;
+    const size_t meta_off = crc_off + round_up(4 * static_cast<size_t>(n), 256);
+    const size_t need = meta_off + (meta_out ? 4 * n_meta * n : 0);
+    Lease L;
+    RET(lease_any(L));
+    RET(slot_reserve(*L.s, need));
+    cudaStream_t st = L.s->stream;
+    uint8_t *db = L.s->dbuf;
+    // H2D: the contiguous input becomes k pitched rows; the tail of the last rows is zero padding
+    const size_t full_rows = len / S, rem = len - full_rows * S;
+    if (full_rows) CK(cudaMemcpy2DAsync(db, pitch, data, S, S, full_rows, cudaMemcpyHostToDevice, st));
+    if (rem) CK(cudaMemcpyAsync(db + full_rows * pitch, data + full_rows * S, rem, cudaMemcpyHostToDevice, st));
+    for (size_t r = full_rows; r < static_cast<size_t>(k); r++) {
+        const size_t o = (r == full_rows) ? rem : 0;
+        CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
+    }
+    gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
+    RET(encode_dev_impl(*L.d, sv, k, m, st));
+    const bool want_crc = shard_crc_out || full_crc_out;
+    std::vector<uint32_t> crc_tmp;
+    if (want_crc) {
+        CrcJob j;
+        j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 0;
+        j.out = reinterpret_cast<uint32_t *>(db + crc_off); j.out_stride = 1;
+        RET(launch_crc(*L.d, j, st));
+        crc_tmp.resize(n);
+        CK(cudaMemcpyAsync(crc_tmp.data(), db + crc_off, 4 * static_cast<size_t>(n), cudaMemcpyDeviceToHost, st));
+    }
+    if (meta_out) {
+        CrcJob j;
+        j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 512;
+        j.out = reinterpret_cast<uint32_t *>(db + meta_off); j.out_stride = n_meta; j.big_endian = 1;
+        RET(launch_crc(*L.d, j, st));
+        for (int i = 0; i < n; i++)
+            if (meta_out[i]) CK(cudaMemcpyAsync(meta_out[i], db + meta_off + 4 * n_meta * i, 4 * n_meta, cudaMemcpyDeviceToHost, st));
+    }
+    for (int r = 0; r < m; r++) {
+        if (!shards_out[k + r]) return GPU_EC_ERR_INVALID_ARG;
+        CK(cudaMemcpyAsync(shards_out[k + r], db + static_cast<size_t>(k + r) * pitch, S, cudaMemcpyDeviceToHost, st));
+    }
+    // systematic data shards are the padded input verbatim (erasure.rs:17-19): host copy while the GPU works
+    for (int j = 0; j < k; j++) {
+        if (!shards_out[j]) return GPU_EC_ERR_INVALID_ARG;
+        const size_t off = static_cast<size_t>(j) * S;
+        const size_t have = off < len ? std::min(S, len - off) : 0;
+        if (have) memcpy(shards_out[j], data + off, have);
+        if (have < S) memset(shards_out[j] + have, 0, S - have);
+    }
+    CK(cudaStreamSynchronize(st));
+    if (shard_crc_out) memcpy(shard_crc_out, crc_tmp.data(), 4 * static_cast<size_t>(n));
+    if (full_crc_out) *full_crc_out = full_crc_host(crc_tmp.data(), S, len, GPU_EC_POLY_IEEE);
+    return GPU_EC_OK;
+}
+
+int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m) {
+    if (!shards || !present) return GPU_EC_ERR_INVALID_ARG;
+    DecodePlan plan;
+    bool noop = false;
+    RET(reconstruct_plan(k, m, present, plan, noop));
+    if (noop) return GPU_EC_OK;
+    if (shard_len == 0) return GPU_EC_ERR_EMPTY_SHARD;
+    const int n = k + m;
+    const size_t S = shard_len, pitch = round_up(S, 256);
+    Lease L;
+    RET(lease_any(L));
+    RET(slot_reserve(*L.s, static_cast<size_t>(n) * pitch));
+    cudaStream_t st = L.s->stream;
+    uint8_t *db = L.s->dbuf;
+    for (int j = 0; j < k; j++) {
+        const int idx = plan.survivors[j];
+        if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
+        CK(cudaMemcpyAsync(db + static_cast<size_t>(idx) * pitch, shards[idx], S, cudaMemcpyHostToDevice, st));
+    }
+    gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
+    RET(launch_apply(*L.d, sv, plan.rows.data(), plan.survivors.data(), k, plan.missing.data(),
+                     static_cast<int>(plan.missing.size()), st));
+    for (int idx : plan.missing) {
+        if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
+        CK(cudaMemcpyAsync(shards[idx], db + static_cast<size_t>(idx) * pitch, S, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    return GPU_EC_OK;
+}
+
+int gpu_ec_decode(uint8_t *const *shards, uint8_t *present, size_t shard_len, int k, int m, size_t original_len,
+                  uint8_t *out) {
+    if (!shards || !present || (!out && original_len)) return GPU_EC_ERR_INVALID_ARG;
+    RET(gpu_ec_reconstruct(shards, present, shard_len, k, m));
+    for (int i = 0; i < k + m; i++) present[i] = 1;
+    size_t left = std::min(original_len, shard_len * static_cast<size_t>(k));  // Vec::truncate never grows
+    for (int j = 0; j < k && left; j++) {
+        const size_t c = std::min(left, shard_len);
+        memcpy(out + static_cast<size_t>(j) * shard_len, shards[j], c);
+        left -= c;
+    }
+    return GPU_EC_OK;
+}
+
+static int crc_host_common(const uint8_t *data, size_t len, size_t chunk, int poly, uint32_t *whole_out,
+                           uint32_t *chunk_out, const uint8_t *meta_be, int64_t *first_bad) {
+    const size_t nchunks = chunk ? div_up(len, chunk) : 0;
+    const size_t data_cap = round_up(len, 256);
+    const size_t crc_off = data_cap;
+    const size_t whole_off = crc_off + round_up(4 * nchunks, 256);
+    const size_t meta_off = whole_off + 256;
+    const size_t need = meta_off + round_up(4 * nchunks, 256) + 256;
+    Lease L;
+    RET(lease_any(L));
+    RET(slot_reserve(*L.s, need));
+    cudaStream_t st = L.s->stream;
+    uint8_t *db = L.s->dbuf;
+    if (len) CK(cudaMemcpyAsync(db, data, len, cudaMemcpyHostToDevice, st));
+    uint32_t *d_chunks = reinterpret_cast<uint32_t *>(db + crc_off);
+    uint32_t *d_whole = reinterpret_cast<uint32_t *>(db + whole_off);
+    unsigned long long *d_bad = reinterpret_cast<unsigned long long *>(db + whole_off + 8);
+    if (meta_be) {
+        if (nchunks) CK(cudaMemcpyAsync(db + meta_off, meta_be, 4 * nchunks, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(d_bad, 0xFF, 8, st));
+    }
+    if (chunk && nchunks) {
+        CrcJob j;
+        j.base = db; j.n_buf = 1; j.buf_stride = data_cap; j.len = len; j.chunk = chunk; j.poly = poly;
+        j.out = d_chunks; j.out_stride = nchunks;
+        if (meta_be) { j.expect_be = db + meta_off; j.first_bad = d_bad; }
+        RET(launch_crc(*L.d, j, st));
+        if (chunk_out) CK(cudaMemcpyAsync(chunk_out, d_chunks, 4 * nchunks, cudaMemcpyDeviceToHost, st));
+    }
+    if (whole_out) {
+        if (chunk && nchunks) {  // fold the chunk CRCs: the bytes were read once (chunkserver.rs:746-769 + 195)
+            CrcJob j;
+            j.poly = poly; j.out = d_whole; j.out_stride = 1;
+            RET(launch_combine(*L.d, d_chunks, 1, nchunks, chunk, len, nchunks, j, st));
+        } else {
+            CrcJob j;
+            j.base = db; j.n_buf = 1; j.buf_stride = data_cap; j.len = len; j.chunk = 0; j.poly = poly;
+            j.out = d_whole; j.out_stride = 1;
+            RET(launch_crc(*L.d, j, st));
+        }
+        CK(cudaMemcpyAsync(whole_out, d_whole, 4, cudaMemcpyDeviceToHost, st));
+    }
+    unsigned long long bad = ~0ull;
+    if (meta_be) CK(cudaMemcpyAsync(&bad, d_bad, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (meta_be) {
+        if (first_bad) *first_bad = (bad == ~0ull) ? -1 : static_cast<int64_t>(bad);
+        if (bad != ~0ull) return GPU_EC_ERR_CRC_MISMATCH;
+    }
+    return GPU_EC_OK;
+}
+
+int gpu_ec_crc32(const uint8_t *data, size_t len, int poly, uint32_t *out) {
+    if (!out || (!data && len) || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    return crc_host_common(data, len, 0, poly, out, nullptr, nullptr, nullptr);
+}
+
+int gpu_ec_crc32_chunks(const uint8_t *data, size_t len, size_t chunk, int poly, uint32_t *out) {
+    if ((!out && len) || (!data && len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    if (len == 0) { RET(ensure_init()); return GPU_EC_OK; }  // zero chunks, empty .meta (chunkserver.rs:184)
+    return crc_host_common(data, len, chunk, poly, nullptr, out, nullptr, nullptr);
+}
+
+int gpu_ec_verify_chunks(const uint8_t *data, size_t len, size_t chunk, int poly, const uint8_t *meta_be,
+                         size_t meta_len, int64_t *first_bad) {
+    if ((!data && len) || (!meta_be && meta_len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    if (first_bad) *first_bad = -1;
+    RET(ensure_init());
+    const size_t n_exp = meta_len / 4, n_act = div_up(len, chunk);  // chunks_exact(4) drops a ragged tail
+    if (n_exp != n_act) return GPU_EC_ERR_COUNT_MISMATCH;           // chunkserver.rs:277-279
+    if (n_act == 0) return GPU_EC_OK;
+    return crc_host_common(data, len, chunk, poly, nullptr, nullptr, meta_be, first_bad);
+}
+
+int gpu_ec_block_checksums(const uint8_t *data, size_t len, size_t chunk, int poly, uint32_t *whole_crc_out,
+                           uint32_t *chunk_crc_out) {
+    if ((!data && len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    if (len == 0) { RET(ensure_init()); if (whole_crc_out) *whole_crc_out = 0; return GPU_EC_OK; }
+    return crc_host_common(data, len, chunk, poly, whole_crc_out, chunk_crc_out, nullptr, nullptr);
+}
+
+// ---- batches: stripe i -> device i mod G, several slots (streams) per device in flight --------
+namespace {
+struct BatchLanes {
+    std::vector<Lease> leases;  // [dev][slot]
+    int per_dev = 0;
+    std::vector<Dev *> devs;
+    int acquire(int slots_per_dev) {
+        RET(ensure_init());
+        std::vector<int> act;
+        { Ctx &c = ctx(); std::lock_guard<std::mutex> lk(c.mu); act = c.active; }
+        per_dev = slots_per_dev;
+        leases.resize(act.size() * slots_per_dev);
+        for (size_t a = 0; a < act.size(); a++) {
+            Dev *d;
+            RET(get_dev(act[a], &d));
+            devs.push_back(d);
+            for (int s = 0; s < slots_per_dev; s++) RET(lease_on(*d, leases[a * slots_per_dev + s]));
+        }
+        return GPU_EC_OK;
+    }
+    int sync_all() {
+        for (auto &l : leases) if (l.s) { CK(cudaSetDevice(l.d->ordinal)); CK(cudaStreamSynchronize(l.s->stream)); }
+        return GPU_EC_OK;
+    }
+};
+}  // namespace
+
+int gpu_ec_encode_batch(const uint8_t *data, size_t stripe_len, size_t n_stripes, int k, int m,
+                        uint8_t *parity_out, uint32_t *shard_crc_out, uint32_t *full_crc_out) {
+    if (k <= 0 || m <= 0) return GPU_EC_ERR_ZERO_SHARDS;
+    if (stripe_len == 0) return GPU_EC_ERR_EMPTY_DATA;
+    if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;
+    if (!data || !parity_out) return GPU_EC_ERR_INVALID_ARG;
+    if (n_stripes == 0) return GPU_EC_OK;
+    const int n = k + m;
+    const size_t S = gpu_ec_shard_len(stripe_len, k), pitch = round_up(S, 256);
+    const size_t crc_off = static_cast<size_t>(n) * pitch;
+    const size_t need = crc_off + round_up(4 * static_cast<size_t>(n) + 4, 256);
+    const bool want_crc = shard_crc_out || full_crc_out;
+    BatchLanes B;
+    RET(B.acquire(3));
+    for (auto &l : B.leases) { CK(cudaSetDevice(l.d->ordinal)); RET(slot_reserve(*l.s, need)); }
+    FullCrcParams f;
+    memset(&f, 0, sizeof f);
+    if (full_crc_out) full_crc_constants(f, S, stripe_len, GPU_EC_POLY_IEEE);
+    const size_t G = B.devs.size();
+    const size_t full_rows = stripe_len / S, rem = stripe_len - full_rows * S;
+    for (size_t i = 0; i < n_stripes; i++) {
+        const size_t di = i % G;
+        Lease &l = B.leases[di * B.per_dev + (i / G) % B.per_dev];
+        CK(cudaSetDevice(l.d->ordinal));
+        cudaStream_t st = l.s->stream;
+        uint8_t *db = l.s->dbuf;
+        const uint8_t *src = data + i * stripe_len;
+        if (full_rows) CK(cudaMemcpy2DAsync(db, pitch, src, S, S, full_rows, cudaMemcpyHostToDevice, st));
+        if (rem) CK(cudaMemcpyAsync(db + full_rows * pitch, src + full_rows * S, rem, cudaMemcpyHostToDevice, st));
+        for (size_t r = full_rows; r < static_cast<size_t>(k); r++) {
+            const size_t o = (r == full_rows) ? rem : 0;
+            CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
+        }
+        gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
+        RET(encode_dev_impl(*l.d, sv, k, m, st));
+        CK(cudaMemcpy2DAsync(parity_out + i * static_cast<size_t>(m) * S, S, db + static_cast<size_t>(k) * pitch, pitch, S, m,
+                             cudaMemcpyDeviceToHost, st));
+        if (want_crc) {
+            uint32_t *d_crc = reinterpret_cast<uint32_t *>(db + crc_off);
+            CrcJob j;
+            j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 0; j.out = d_crc; j.out_stride = 1;
+            RET(launch_crc(*l.d, j, st));
+            if (shard_crc_out) CK(cudaMemcpyAsync(shard_crc_out + i * n, d_crc, 4 * static_cast<size_t>(n), cudaMemcpyDeviceToHost, st));
+            if (full_crc_out) {
+                f.shard_crc = d_crc; f.full_crc = d_crc + n; f.n_stripes = 1; f.n_shards = n;
+                stripe_full_crc_kernel<<<1, 32, 0, st>>>(f);
+                g_launches++;
+                CK(cudaGetLastError());
+                CK(cudaMemcpyAsync(full_crc_out + i, d_crc + n, 4, cudaMemcpyDeviceToHost, st));
+            }
+        }
+    }
+    return B.sync_all();
+}
+
+int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t shard_len, size_t n_stripes, int k, int m) {
+    if (!shards || !present) return GPU_EC_ERR_INVALID_ARG;
+    DecodePlan plan;
+    bool noop = false;
+    RET(reconstruct_plan(k, m, present, plan, noop));
+    if (noop || n_stripes == 0) return GPU_EC_OK;
+    if (shard_len == 0) return GPU_EC_ERR_EMPTY_SHARD;
+    const int n = k + m;
+    const size_t S = shard_len, pitch = round_up(S, 256);
+    const size_t host_stripe = static_cast<size_t>(n) * S, dev_stripe = static_cast<size_t>(n) * pitch;
+    // groups of stripes per transfer: one 2-D copy per surviving / rebuilt slot per group
+    const size_t grp = std::max<size_t>(1, std::min<size_t>(n_stripes, (48ull << 20) / host_stripe));
+    BatchLanes B;
+    RET(B.acquire(3));
+    for (auto &l : B.leases) { CK(cudaSetDevice(l.d->ordinal)); RET(slot_reserve(*l.s, grp * dev_stripe)); }
+    const size_t G = B.devs.size();
+    size_t gi = 0;
+    for (size_t i0 = 0; i0 < n_stripes; i0 += grp, gi++) {
+        const size_t cnt = std::min(grp, n_stripes - i0);
+        Lease &l = B.leases[(gi % G) * B.per_dev + (gi / G) % B.per_dev];
+        CK(cudaSetDevice(l.d->ordinal));
+        cudaStream_t st = l.s->stream;
+        uint8_t *db = l.s->dbuf;
+        uint8_t *hb = shards + i0 * host_stripe;
+        for (int j = 0; j < k; j++) {
+            const size_t idx = plan.survivors[j];
+            CK(cudaMemcpy2DAsync(db + idx * pitch, dev_stripe, hb + idx * S, host_stripe, S, cnt, cudaMemcpyHostToDevice, st));
+        }
+        gpu_ec_stripes sv{db, pitch, dev_stripe, S, cnt};
+        RET(launch_apply(*l.d, sv, plan.rows.data(), plan.survivors.data(), k, plan.missing.data(),
+                         static_cast<int>(plan.missing.size()), st));
+        for (int idx : plan.missing)
+            CK(cudaMemcpy2DAsync(hb + static_cast<size_t>(idx) * S, host_stripe, db + static_cast<size_t>(idx) * pitch, dev_stripe, S, cnt,
+                                 cudaMemcpyDeviceToHost, st));
+    }
+    return B.sync_all();
+}
+
+}  // extern "C"

@@ -1,0 +1,263 @@
+// rs_kernels.cuh — Reed-Solomon GF(2^8) "apply matrix" kernels for sm_100a.
+//
+// One kernel family serves both encode (reference: reed-solomon-erasure `encode`, call site
+// dfs/common/src/erasure.rs:21) and reconstruct (`reconstruct`, erasure.rs:38 and
+// dfs/chunkserver/src/chunkserver.rs:620-623): out_r = XOR_j coef[r][j] * in_j over GF(2^8),
+// with the host-composed decode rows for reconstruct, so both are ONE pass: read n_in shards,
+// write n_out shards.
+//
+// The path is HBM-bound byte work (no tensor cores). GF multiply-by-constant is a table lookup;
+// B200 has no GF/CLMUL instruction, so the binding resource is the shared-memory crossbar
+// (32 lookups/clk/SM). Design choices that follow from that:
+//   * rs_lut8: ONE lookup per data byte regardless of n_out<=4: a 256-entry table per input
+//     shard whose u32 entry packs the products for all 4 output rows; the table is replicated
+//     per lane (word index = entry*32 + lane) so every LDS is bank-conflict-free. 32 KiB per
+//     input shard -> n_in <= 7 in the 227 KiB of one SM.
+//   * rs_lut4: split-nibble variant (two 16-entry packed tables per input shard, 4 KiB per
+//     shard, lane-replicated, 2 lookups per byte) for n_in up to 56 per pass, with an
+//     accumulate flag so wider codes (k+m <= 256) are covered in several passes.
+//   * 16-byte coalesced loads straight into registers (no reuse -> no smem staging needed),
+//     next tile prefetched before the current one is computed, XOR-accumulate in registers,
+//     4x4 byte transpose with PRMT, 16-byte coalesced stores: each byte crosses HBM once.
+//   * persistent grid: one CTA per SM (the table owns the SM's shared memory), tiles strided.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "lut_common.cuh"
+
+namespace gpu_ec {
+
+constexpr int RS_THREADS = 512;
+constexpr int RS_MAX_OUT = 4;        // output rows per pass (packed into one u32 entry)
+constexpr int RS_LUT8_MAX_IN = 7;    // 7 * 32 KiB = 224 KiB
+constexpr int RS_LUT4_MAX_IN = 56;   // 56 * 4 KiB = 224 KiB
+
+struct RsParams {
+    uint8_t *base;
+    unsigned long long shard_stride;
+    unsigned long long stripe_stride;
+    unsigned long long n_tiles;       // n_stripes * tiles_per_stripe
+    unsigned int nvec;                // 16-byte vectors per shard = ceil(shard_len / 16)
+    unsigned int tiles_per_stripe;    // ceil(nvec / RS_THREADS)
+    int n_in;
+    int n_out;
+    int accumulate;                   // XOR into the existing output instead of overwriting
+    int in_idx[RS_LUT4_MAX_IN];
+    int out_idx[RS_MAX_OUT];
+    uint8_t coef[RS_MAX_OUT][RS_LUT4_MAX_IN];
+};
+
+__device__ __forceinline__ uint32_t gf_mul_dev(uint32_t a, uint32_t b) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        r ^= (b & 1u) ? a : 0u;
+        a <<= 1;
+        a ^= (a & 0x100u) ? 0x11Du : 0u;
+        b >>= 1;
+    }
+    return r & 0xffu;
+}
+
+// packed products of byte value `x` with the coefficients of input column j for all output rows
+__device__ __forceinline__ uint32_t packed_products(const RsParams &p, int j, uint32_t x) {
+    uint32_t v = 0;
+#pragma unroll
+    for (int r = 0; r < RS_MAX_OUT; r++)
+        if (r < p.n_out) v |= gf_mul_dev(p.coef[r][j], x) << (8 * r);
+    return v;
+}
+
+// acc[4] hold, for 4 consecutive data byte positions, {row0,row1,row2,row3} product bytes.
+// Returns word `r` of the transposed 4x4: the 4 consecutive bytes of output row r.
+__device__ __forceinline__ void transpose4x4(const uint32_t a[4], uint32_t o[4]) {
+    uint32_t t0 = __byte_perm(a[0], a[1], 0x5140);  // a0.b0 a1.b0 a0.b1 a1.b1
+    uint32_t t1 = __byte_perm(a[0], a[1], 0x7362);  // a0.b2 a1.b2 a0.b3 a1.b3
+    uint32_t t2 = __byte_perm(a[2], a[3], 0x5140);
+    uint32_t t3 = __byte_perm(a[2], a[3], 0x7362);
+    o[0] = __byte_perm(t0, t2, 0x5410);
+    o[1] = __byte_perm(t0, t2, 0x7632);
+    o[2] = __byte_perm(t1, t3, 0x5410);
+    o[3] = __byte_perm(t1, t3, 0x7632);
+}
+
+__device__ __forceinline__ uint4 ld_vec(const uint8_t *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+
+// ---------------------------------------------------------------------------------------------
+// rs_lut8: full-byte packed LUT, lane-replicated, n_in = K <= 7.
+// Algorithmic bytes per tile: (K + n_out) * 16 * RS_THREADS; one LDS per input byte.
+template <int K>
+__global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_constant__ RsParams p) {
+    extern __shared__ __align__(16) uint32_t rs_tab[];  // [K][256][32]
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    constexpr int NW = RS_THREADS / 32;
+
+    // build the table: each lane computes one entry, the warp broadcasts it into the 32 lane copies
+    for (int e0 = warp * 32; e0 < K * 256; e0 += NW * 32) {
+        const int e = e0 + lane;
+        const uint32_t v = packed_products(p, e >> 8, static_cast<uint32_t>(e & 255));
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) rs_tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+    }
+    __syncthreads();
+
+    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab)) + lane * 4;
+    const unsigned long long step = gridDim.x;
+    unsigned long long t = blockIdx.x;
+    if (t >= p.n_tiles) return;
+
+    uint4 cur[K];
+    bool cur_ok;
+    unsigned long long cur_off;
+    auto locate = [&](unsigned long long tile, unsigned long long &off) -> bool {
+        const unsigned long long stripe = tile / p.tiles_per_stripe;
+        const unsigned int tt = static_cast<unsigned int>(tile - stripe * p.tiles_per_stripe);
+        const unsigned int v = tt * RS_THREADS + threadIdx.x;
+        off = stripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+        return v < p.nvec;
+    };
+    auto load = [&](uint4 (&d)[K], unsigned long long off, bool ok) {
+#pragma unroll
+        for (int j = 0; j < K; j++)
+            d[j] = ok ? ld_vec(p.base + off + static_cast<unsigned long long>(p.in_idx[j]) * p.shard_stride)
+                      : make_uint4(0, 0, 0, 0);
+    };
+    cur_ok = locate(t, cur_off);
+    load(cur, cur_off, cur_ok);
+
+    for (; t < p.n_tiles; t += step) {
+        uint4 nxt[K];
+        unsigned long long nxt_off = 0;
+        bool nxt_ok = false;
+        if (t + step < p.n_tiles) nxt_ok = locate(t + step, nxt_off);
+        load(nxt, nxt_off, nxt_ok);
+
+        if (cur_ok) {
+            uint32_t acc[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) acc[i] = 0;
+#pragma unroll
+            for (int j = 0; j < K; j++) {
+                const uint32_t tj = tl + j * (256 * 32 * 4);
+                const uint32_t w[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
+                    acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
+                    acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
+                    acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
+                }
+            }
+            uint32_t o[4][4];  // o[q][r]
+#pragma unroll
+            for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
+#pragma unroll
+            for (int r = 0; r < RS_MAX_OUT; r++) {
+                if (r < p.n_out) {
+                    uint4 *dst = reinterpret_cast<uint4 *>(p.base + cur_off + static_cast<unsigned long long>(p.out_idx[r]) * p.shard_stride);
+                    uint4 v = make_uint4(o[0][r], o[1][r], o[2][r], o[3][r]);
+                    if (p.accumulate) { const uint4 old = *dst; v.x ^= old.x; v.y ^= old.y; v.z ^= old.z; v.w ^= old.w; }
+                    *dst = v;
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < K; j++) cur[j] = nxt[j];
+        cur_ok = nxt_ok;
+        cur_off = nxt_off;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rs_lut4: split-nibble packed LUTs, lane-replicated, any n_in <= 56 per pass.
+// smem word index: ((j*2 + half)*16 + nibble)*32 + lane. Two LDS per input byte.
+__global__ void __launch_bounds__(RS_THREADS, 1) rs_lut4_kernel(const __grid_constant__ RsParams p) {
+    extern __shared__ __align__(16) uint32_t rs_tab[];  // [n_in][2][16][32]
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    constexpr int NW = RS_THREADS / 32;
+    const int n_entries = p.n_in * 32;
+    for (int e0 = warp * 32; e0 < n_entries; e0 += NW * 32) {
+        const int e = e0 + lane;  // e = (j*2 + half)*16 + nibble
+        const int j = e >> 5;
+        const uint32_t x = (e & 16) ? static_cast<uint32_t>((e & 15) << 4) : static_cast<uint32_t>(e & 15);
+        const uint32_t v = packed_products(p, j, x);
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) rs_tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+    }
+    __syncthreads();
+
+    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab)) + lane * 4;
+    for (unsigned long long t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+        const unsigned long long stripe = t / p.tiles_per_stripe;
+        const unsigned int tt = static_cast<unsigned int>(t - stripe * p.tiles_per_stripe);
+        const unsigned int v = tt * RS_THREADS + threadIdx.x;
+        if (v >= p.nvec) continue;
+        const unsigned long long off = stripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+        uint32_t acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) acc[i] = 0;
+        for (int j0 = 0; j0 < p.n_in; j0 += 4) {
+            uint4 d[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                d[u] = (j0 + u < p.n_in)
+                           ? ld_vec(p.base + off + static_cast<unsigned long long>(p.in_idx[j0 + u]) * p.shard_stride)
+                           : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (j0 + u < p.n_in) {
+                    const uint32_t tj = tl + (j0 + u) * (2 * 16 * 32 * 4);
+                    const uint32_t w[4] = {d[u].x, d[u].y, d[u].z, d[u].w};
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        const uint32_t lo4 = w[q] & 0x0f0f0f0fu, hi4 = (w[q] >> 4) & 0x0f0f0f0fu;
+                        acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(lo4)) ^ lut_lds<2048>(tj, byte_of<0>(hi4));
+                        acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(lo4)) ^ lut_lds<2048>(tj, byte_of<1>(hi4));
+                        acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(lo4)) ^ lut_lds<2048>(tj, byte_of<2>(hi4));
+                        acc[q * 4 + 3] ^= lut_lds<0>(tj, lo4 >> 24) ^ lut_lds<2048>(tj, hi4 >> 24);
+                    }
+                }
+            }
+        }
+        uint32_t o[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
+#pragma unroll
+        for (int r = 0; r < RS_MAX_OUT; r++) {
+            if (r < p.n_out) {
+                uint4 *dst = reinterpret_cast<uint4 *>(p.base + off + static_cast<unsigned long long>(p.out_idx[r]) * p.shard_stride);
+                uint4 val = make_uint4(o[0][r], o[1][r], o[2][r], o[3][r]);
+                if (p.accumulate) { const uint4 old = *dst; val.x ^= old.x; val.y ^= old.y; val.z ^= old.z; val.w ^= old.w; }
+                *dst = val;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// synthetic data: byte i = byte (i%8) of splitmix64(seed ^ (i/8))
+__device__ __forceinline__ unsigned long long splitmix64_dev(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+// out must be 8-byte aligned and byte_offset a multiple of 8 (checked by the host wrapper)
+__global__ void fill_synthetic_kernel(uint8_t *out, unsigned long long len, unsigned long long seed,
+                                      unsigned long long byte_offset) {
+    const unsigned long long nwords = (len + 7) / 8;
+    for (unsigned long long w = blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x; w < nwords;
+         w += static_cast<unsigned long long>(gridDim.x) * blockDim.x) {
+        const unsigned long long v = splitmix64_dev(seed ^ ((byte_offset >> 3) + w));
+        if ((w + 1) * 8 <= len) {
+            reinterpret_cast<unsigned long long *>(out)[w] = v;
+        } else {
+            for (unsigned long long i = w * 8; i < len; i++) out[i] = static_cast<uint8_t>(v >> (8 * (i & 7)));
+        }
+    }
+}
+
+}  // namespace gpu_ec
