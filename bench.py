@@ -280,7 +280,7 @@ def main():
         S4 = gpu_ec.erasure.shard_len(64 << 20, 10)
         n4 = 48
         b4 = device.StripeBatch(n4, 10, 4, S4)
-        b4.fill_synthetic(0xEC000004 + rank)
+        b4.fill_synthetic(0xEC000004 + rank, original_len=64 << 20)
         crc4, full4 = b4.encode_crc(original_len=64 << 20)
         torch.cuda.synchronize()
         d0 = np.concatenate([b4.shard_host(0, j) for j in range(10)])

@@ -320,7 +320,7 @@ def test_dev_encode_reconstruct_crc(L, orc, k, m, stripe_len, n_stripes):
     from gpu_ec import device
     S = erasure.shard_len(stripe_len, k)
     b = device.StripeBatch(n_stripes, k, m, S)
-    b.fill_synthetic(0xEC0000AA)
+    b.fill_synthetic(0xEC0000AA, original_len=stripe_len)
     torch.cuda.synchronize()
     data0 = [b.shard_host(0, j) for j in range(k)]
     assert np.array_equal(data0[1], orc.fill_synthetic(S, 0xEC0000AA, 1 * b.pitch))
