@@ -162,6 +162,19 @@ int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int 
  * (full_crc is derived from the shard CRCs with that assumption, not from a second data pass). */
 int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original_len, int poly,
                           uint32_t *shard_crc, uint32_t *full_crc, void *stream);
+/* No counterpart in the reference. Same result as gpu_ec_crc32_dev (whole-buffer CRC of each of
+ * n_buf device buffers -> out[b]) for callers that must not allocate: processes whose device
+ * memory is budgeted once at start-up, latency paths that cannot risk an allocator call, and
+ * work that is recorded for replay. The per-segment CRCs that gpu_ec_crc32_dev keeps in
+ * stream-ordered scratch live here in a 4 MiB array built into the library (held by every GPU
+ * that loads it), so: at most 2^20 segments per call (n_buf * ceil(len / segment), segment grown
+ * up to 64 KiB to fit; larger calls return GPU_EC_ERR_INVALID_ARG with an explanatory
+ * gpu_ec_last_error()); calls that may overlap on one GPU race on that array and must be
+ * serialised; the first call on a device performs a one-time set-up (address look-up, table
+ * upload) and should be made before any stream capture begins. No cudaMalloc/cudaFree or other
+ * allocating routine is called. */
+int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, int poly,
+                             uint32_t *out, void *stream);
 /* synthetic bytes: byte i = byte (i%8) of splitmix64(seed ^ (i/8)), i counted from byte_offset */
 int gpu_ec_fill_synthetic_dev(uint8_t *out, size_t len, uint64_t seed, uint64_t byte_offset, void *stream);
 

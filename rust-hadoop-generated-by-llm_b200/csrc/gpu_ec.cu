@@ -1031,4 +1031,139 @@ int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t sha
     return B.sync_all();
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// gpu_ec_crc32_dev_noalloc — whole-buffer CRCs for callers that are not allowed to allocate.
+//
+// gpu_ec_crc32_dev hashes each buffer as many short segments and parks the per-segment CRCs in
+// scratch that it takes from the stream-ordered allocator. Some callers cannot do that: code
+// that runs where the process's device-memory budget is fixed up front (a storage daemon that
+// pre-sizes its HBM pools and treats any later allocation as a fault), code on a latency path
+// where an allocator call may block behind another thread or trim/grow a pool, and code that
+// records its work for replay, where an allocation would be baked into the recording. For them
+// the per-segment CRCs go into the fixed array below, which is part of the library image: each
+// GPU that loads libgpu_ec.so holds these 4 MiB from load until the process exits.
+//
+// Consequences of sharing one array between all calls:
+//   * the capacity is fixed: n_buf * ceil(len / segment) must not exceed NOALLOC_MAX_PARTIALS.
+//     The segment length is raised (up to 64 KiB) to make large inputs fit; beyond that the call
+//     is refused with GPU_EC_ERR_INVALID_ARG and gpu_ec_last_error() says why;
+//   * the array still holds the previous call's values. Nothing in it has to start at zero:
+//     every slot the fold kernel reads is written by the segment kernel earlier in the same call,
+//     on the same stream, so stale contents are never observed and no clearing pass is issued;
+//   * two calls whose kernels can be in flight at the same time on one GPU (different streams,
+//     or different host threads) would overwrite each other's partials. Serialise them.
+//
+// The first call on each device does a one-time set-up with that device current: it resolves the
+// device address of the array (the host-side name is only a handle, not something a kernel can
+// dereference), uploads the CRC tables into their static symbol and raises the kernel's
+// shared-memory limit. Make that first call before starting any stream capture.
+// It never calls cudaMalloc / cudaFree / cudaMallocAsync / cudaFreeAsync or any other allocating
+// routine, and it creates no streams or events.
+namespace {
+constexpr size_t NOALLOC_MAX_PARTIALS = size_t(1) << 20;  // 4 MiB of u32 per-segment CRCs
+constexpr size_t NOALLOC_MAX_SEGMENT = 65536;
+}  // namespace
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_MAX_PARTIALS];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct NoAllocDev {
+    std::mutex mu;
+    bool ready = false;
+    uint32_t *scratch = nullptr;  // device address of g_noalloc_scratch on this device
+    Dev shim;                     // only ordinal + sm_count are used (launch_combine sizes its grid from it)
+};
+NoAllocDev g_noalloc_dev[NOALLOC_MAX_DEVICES];
+
+int noalloc_setup(int ordinal, NoAllocDev **out) {
+    if (ordinal < 0 || ordinal >= NOALLOC_MAX_DEVICES) return GPU_EC_ERR_INVALID_ARG;
+    NoAllocDev &nd = g_noalloc_dev[ordinal];
+    std::lock_guard<std::mutex> lk(nd.mu);
+    CK(cudaSetDevice(ordinal));
+    if (!nd.ready) {
+        void *addr = nullptr;
+        CK(cudaGetSymbolAddress(&addr, g_noalloc_scratch));  // per device: each GPU has its own copy
+        if (!addr) { t_last_error = "cudaGetSymbolAddress returned a null scratch address"; return GPU_EC_ERR_CUDA; }
+        int sms = 0;
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ordinal));
+        static uint32_t tabs[2][4][256];
+        static std::once_flag once;
+        std::call_once(once, [] { for (int p = 0; p < 2; p++) crc_tables(kPolyReflected[p], tabs[p]); });
+        CK(cudaMemcpyToSymbol(g_crc_tab, tabs, sizeof tabs));  // same bytes dev_prepare uploads; no allocation
+        CK(cudaFuncSetAttribute(crc_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+        nd.scratch = static_cast<uint32_t *>(addr);
+        nd.shim.ordinal = ordinal;
+        nd.shim.sm_count = sms;
+        nd.ready = true;
+    }
+    *out = &nd;
+    return GPU_EC_OK;
+}
+}  // namespace
+
+int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, int poly,
+                             uint32_t *out, void *stream) {
+    if (!base || !out || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    cudaPointerAttributes attr;
+    CK(cudaPointerGetAttributes(&attr, base));
+    if (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged) {
+        t_last_error = "gpu_ec_crc32_dev_noalloc: base is not device memory";
+        return GPU_EC_ERR_INVALID_ARG;
+    }
+    NoAllocDev *nd = nullptr;
+    RET(noalloc_setup(attr.device, &nd));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_buf == 0) return GPU_EC_OK;
+    if (len == 0) {  // crc32fast of nothing is 0
+        CK(cudaMemsetAsync(out, 0, 4 * n_buf, st));
+        return GPU_EC_OK;
+    }
+    CrcJob j;
+    j.base = base; j.n_buf = n_buf; j.buf_stride = buf_stride; j.len = len; j.chunk = 0; j.poly = poly;
+    j.out = out; j.out_stride = 1;
+    const int sms = nd->shim.sm_count;
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (buf_stride & 15)) {
+        // unaligned buffers take the one-thread-per-buffer kernel, which needs no scratch at all
+        CrcSlowParams sp;
+        memset(&sp, 0, sizeof sp);
+        sp.base = base; sp.buf_stride = buf_stride; sp.n_buf = n_buf; sp.len = len; sp.chunk = len; sp.chunks_per_buf = 1;
+        sp.out = out; sp.out_stride = 1; sp.poly = poly;
+        const int grid = static_cast<int>(std::min<size_t>(div_up(n_buf, 128), static_cast<size_t>(sms) * 16));
+        crc_chunks_slow_kernel<<<grid, 128, 0, st>>>(sp);
+        g_launches++;
+        CK(cudaGetLastError());
+        return GPU_EC_OK;
+    }
+    // shortest segment (most parallelism) whose partial count fits the fixed array
+    size_t G = 512;
+    while (G <= NOALLOC_MAX_SEGMENT && n_buf * div_up(len, G) > NOALLOC_MAX_PARTIALS) G *= 2;
+    if (G > NOALLOC_MAX_SEGMENT) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "gpu_ec_crc32_dev_noalloc: %zu buffers x %zu bytes need more than the %zu per-segment slots of the "
+                 "built-in scratch even at %zu-byte segments; split the batch or use gpu_ec_crc32_dev",
+                 n_buf, len, NOALLOC_MAX_PARTIALS, NOALLOC_MAX_SEGMENT);
+        t_last_error = msg;
+        return GPU_EC_ERR_INVALID_ARG;
+    }
+    CrcParams p;
+    memset(&p, 0, sizeof p);
+    p.base = base; p.buf_stride = buf_stride; p.n_buf = n_buf; p.len = len;
+    p.G = static_cast<unsigned int>(G);
+    p.nfull = len / G;
+    p.rag = static_cast<unsigned int>(len % G);
+    p.segs_per_buf = p.nfull + (p.rag ? 1 : 0);
+    p.tiles_per_buf = div_up(p.nfull, 32);
+    p.poly = poly;
+    p.out = nd->scratch;  // the device address, never the host-side symbol
+    p.out_stride = p.segs_per_buf;
+    const unsigned long long warps = n_buf * p.tiles_per_buf + (p.rag ? n_buf : 0);
+    const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(sms))));
+    crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
+    g_launches++;
+    CK(cudaGetLastError());
+    return launch_combine(nd->shim, nd->scratch, n_buf, p.segs_per_buf, G, len, p.segs_per_buf, j, st);
+}
+
 }  // extern "C"

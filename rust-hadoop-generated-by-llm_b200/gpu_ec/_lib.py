@@ -88,6 +88,7 @@ SIGNATURES = {
     "gpu_ec_apply_matrix_dev": (_i, [C.POINTER(Stripes), _vp, _vp, _i, _vp, _i, _vp]),
     "gpu_ec_crc32_chunks_dev": (_i, [_vp, _sz, _sz, _sz, _sz, _i, _vp, _sz, _i, _vp]),
     "gpu_ec_crc32_dev": (_i, [_vp, _sz, _sz, _sz, _i, _vp, _vp]),
+    "gpu_ec_crc32_dev_noalloc": (_i, [_vp, _sz, _sz, _sz, _i, _vp, _vp]),
     "gpu_ec_verify_chunks_dev": (_i, [_vp, _sz, _sz, _i, _vp, _vp, _vp]),
     "gpu_ec_encode_crc_dev": (_i, [C.POINTER(Stripes), _i, _i, _sz, _i, _vp, _vp, _vp]),
     "gpu_ec_fill_synthetic_dev": (_i, [_vp, _sz, _u64, _u64, _vp]),
