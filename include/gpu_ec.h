@@ -156,8 +156,8 @@ int gpu_ec_crc32_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_
 int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int poly,
                              const uint8_t *meta_be, long long *first_bad, void *stream);
 /* encode + CRC-32 of all k+m shards (+ CRC of the original original_len bytes when full_crc is
- * non-NULL; original_len = 0 means k*shard_len) for every stripe, stripe by stripe so the parity
- * is checksummed while still L2-resident. shard_crc: n_stripes*(k+m) words; full_crc: n_stripes.
+ * non-NULL; original_len = 0 means k*shard_len) for every stripe (an encode pass, then a CRC pass
+ * over all shards; full_crc costs no data pass). shard_crc: n_stripes*(k+m) words; full_crc: n_stripes.
  * The bytes of the data slots beyond original_len must be the zero padding of erasure.rs:18
  * (full_crc is derived from the shard CRCs with that assumption, not from a second data pass). */
 int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original_len, int poly,

@@ -12,13 +12,15 @@
 //   * lane = segment: each lane runs the plain serial CRC of its own G-byte segment, so no
 //     per-lane shift tables and no cross-lane fold in the hot loop. A warp owns 32 consecutive
 //     segments and walks them in 128-byte column slices: the slice (32 rows x 128 B) is fetched
-//     with fully coalesced 16-byte loads (8 lanes per 128-byte line), parked in a swizzled
-//     per-warp shared-memory box, and read back row-per-lane with conflict-free LDS.128;
-//     the next slice's loads are in flight while the current one is hashed;
+//     with fully coalesced 16-byte cp.async.cg copies (8 lanes per 128-byte line, straight into a
+//     swizzled per-warp shared-memory box: no register staging, no L1 allocation — with ~200 KiB
+//     of tables + boxes the L1 is tiny and an LDG path through it throttles), and read back
+//     row-per-lane with conflict-free LDS.128; the next slice streams in while this one is hashed;
 //   * chunk sizes above G (64 KiB blocks, whole shards) are hashed as G-byte sub-segments and
-//     folded by crc_combine_kernel using carry-less shift constants (x^(8n) mod P) and warp
+//     folded by crc_fold_kernel using carry-less shift constants (x^(8n) mod P) and warp
 //     shuffles: crc(A||B) = crc(A)*x^(8|B|) xor crc(B) on finalised CRCs;
-//   * the ragged tail of a buffer (len % G bytes) is hashed by one lane straight from global.
+//   * the ragged tail of a buffer (len % G bytes) rides along as one more row of the last tile
+//     (fewer column slices), only its final < 128 bytes are hashed serially by that lane.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -27,11 +29,14 @@
 
 namespace gpu_ec {
 
-constexpr int CRC_WARPS = 16;
+#ifndef GPU_EC_CRC_WARPS
+#define GPU_EC_CRC_WARPS 16
+#endif
+constexpr int CRC_WARPS = GPU_EC_CRC_WARPS;
 constexpr int CRC_THREADS = CRC_WARPS * 32;
 constexpr int CRC_TAB_BYTES = 4 * 256 * 32 * 4;            // 128 KiB
 constexpr int CRC_BOX_BYTES = 32 * 128;                    // per-warp staging box
-constexpr int CRC_SMEM_BYTES = CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES;  // 192 KiB
+constexpr int CRC_SMEM_BYTES = CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES;  // 224 KiB
 
 // slice-by-4 tables for both polynomials, filled once per device by the host (host_math.hpp)
 __device__ uint32_t g_crc_tab[2][4][256];
@@ -43,7 +48,7 @@ struct CrcParams {
     unsigned long long len;            // bytes per buffer
     unsigned long long nfull;          // full G-byte segments per buffer
     unsigned long long segs_per_buf;   // nfull + (rag ? 1 : 0)
-    unsigned long long tiles_per_buf;  // ceil(nfull / 32)
+    unsigned long long tiles_per_buf;  // ceil(segs_per_buf / 32): the ragged segment is a row too
     unsigned int G;                    // segment bytes, multiple of 128
     unsigned int rag;                  // len % G
     uint32_t *out;                     // out[b*out_stride + seg]
@@ -70,8 +75,14 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     uint32_t *tab = reinterpret_cast<uint32_t *>(crc_smem);
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    // replicate the 4 KiB table 32 times: thread i of each group of 32 writes lane copy i
-    for (int e = warp; e < 1024; e += CRC_WARPS) tab[e * 32 + lane] = g_crc_tab[p.poly][e >> 8][e & 255];
+    // replicate the 4 KiB table 32 times: one coalesced global load per lane, then each entry is
+    // broadcast into its 32 lane copies (tab[entry*32 + lane])
+    for (int e0 = warp * 32; e0 < 1024; e0 += CRC_WARPS * 32) {
+        const int e = e0 + lane;
+        const uint32_t v = g_crc_tab[p.poly][e >> 8][e & 255];
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+    }
     __syncthreads();
 
     const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(tab)) + lane * 4;
@@ -85,73 +96,78 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
         return a ^ b ^ d ^ e;
     };
 
-    const unsigned int ncol = p.G >> 7;  // 128-byte column slices per segment
+    const unsigned int ncol = p.G >> 7;        // 128-byte column slices per full segment
+    const unsigned int ncol_rag = p.rag >> 7;  // whole slices of the ragged segment
     const unsigned long long n_tiles = p.n_buf * p.tiles_per_buf;
     const unsigned long long wstep = static_cast<unsigned long long>(gridDim.x) * CRC_WARPS;
-    const unsigned long long w0 = static_cast<unsigned long long>(blockIdx.x) * CRC_WARPS + warp;
     // staging roles: 8 lanes cover one 128-byte row slice, 4 rows per load instruction
     const int srow = lane >> 3, scol = lane & 7;
 
-    unsigned long long tile = w0;
+    unsigned long long tile = static_cast<unsigned long long>(blockIdx.x) * CRC_WARPS + warp;
     unsigned int col = 0;
-    uint4 pre[8];
+    // number of column slices row `seg` of a buffer has
+    auto cols_of = [&](unsigned long long seg) -> unsigned int {
+        return seg < p.nfull ? ncol : (seg == p.nfull ? ncol_rag : 0u);
+    };
+    // global -> shared without touching registers or allocating in L1 (cp.async.cg, 16 bytes per
+    // lane): the box is filled for slice (tl_, c_) while the previous slice is hashed from registers
+    const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
     auto issue_loads = [&](unsigned long long tl_, unsigned int c_) {
         const unsigned long long buf = tl_ / p.tiles_per_buf;
         const unsigned long long seg0 = (tl_ - buf * p.tiles_per_buf) * 32ull;
         const uint8_t *src = p.base + buf * p.buf_stride + seg0 * p.G + static_cast<unsigned long long>(c_) * 128ull + scol * 16;
-        const unsigned long long left = p.nfull - seg0;  // rows available in this tile (may exceed 32)
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             const unsigned int row = i * 4 + srow;
-            pre[i] = (row < left) ? __ldg(reinterpret_cast<const uint4 *>(src + static_cast<unsigned long long>(row) * p.G))
-                                  : make_uint4(0, 0, 0, 0);
+            if (c_ < cols_of(seg0 + row)) {
+                const uint32_t dst = box_s + (row * 8 + (scol ^ (row & 7))) * 16;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + static_cast<unsigned long long>(row) * p.G) : "memory");
+            }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    // a tile whose only row is a short ragged segment may have zero full slices: still one pass
+    const unsigned int ncol_loop = ncol ? ncol : 1u;
     if (tile < n_tiles) issue_loads(tile, 0);
     uint32_t c = 0xFFFFFFFFu;
     while (tile < n_tiles) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
+        // this lane's 128-byte row slice -> registers (conflict-free LDS.128 through the swizzle)
+        uint4 v[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const int row = i * 4 + srow;
-            box[row * 8 + (scol ^ (row & 7))] = pre[i];
-        }
+        for (int q = 0; q < 8; q++) v[q] = box[lane * 8 + (q ^ (lane & 7))];
         __syncwarp();
-        // advance and prefetch
+        // advance; the next slice streams into the box while this one is hashed
         const unsigned long long cur_tile = tile;
-        const bool last_col = (col + 1 == ncol);
+        const unsigned int cur_col = col;
+        const bool last_col = (col + 1 == ncol_loop);
         if (last_col) { tile += wstep; col = 0; } else { col++; }
         if (tile < n_tiles) issue_loads(tile, col);
-        // hash this lane's 128-byte row slice
+        const unsigned long long buf = cur_tile / p.tiles_per_buf;
+        const unsigned long long seg = (cur_tile - buf * p.tiles_per_buf) * 32ull + lane;
+        if (cur_col < cols_of(seg)) {
 #pragma unroll
-        for (int q = 0; q < 8; q++) {
-            const uint4 v = box[lane * 8 + (q ^ (lane & 7))];
-            c = step_word(c, v.x);
-            c = step_word(c, v.y);
-            c = step_word(c, v.z);
-            c = step_word(c, v.w);
+            for (int q = 0; q < 8; q++) {
+                c = step_word(c, v[q].x);
+                c = step_word(c, v[q].y);
+                c = step_word(c, v[q].z);
+                c = step_word(c, v[q].w);
+            }
         }
         if (last_col) {
-            const unsigned long long buf = cur_tile / p.tiles_per_buf;
-            const unsigned long long seg = (cur_tile - buf * p.tiles_per_buf) * 32ull + lane;
-            if (seg < p.nfull) crc_emit(p, buf, seg, ~c);
-            c = 0xFFFFFFFFu;
-        }
-    }
-
-    // ragged tails: one per buffer, hashed serially by lane 0 of a warp straight from global
-    if (p.rag) {
-        for (unsigned long long b = w0; b < p.n_buf; b += wstep) {
-            if (lane == 0) {
-                const uint8_t *src = p.base + b * p.buf_stride + p.nfull * p.G;
-                uint32_t cc = 0xFFFFFFFFu;
+            if (seg < p.nfull) {
+                crc_emit(p, buf, seg, ~c);
+            } else if (seg == p.nfull && p.rag) {
+                // the ragged segment: its last (rag % 128) bytes straight from global
+                const uint8_t *src = p.base + buf * p.buf_stride + p.nfull * p.G + (static_cast<unsigned long long>(ncol_rag) << 7);
+                const unsigned int left = p.rag & 127u;
                 unsigned int i = 0;
-                for (; i + 4 <= p.rag; i += 4) cc = step_word(cc, *reinterpret_cast<const uint32_t *>(src + i));
-                for (; i < p.rag; i++) {
-                    cc = (cc >> 8) ^ lut_lds<0>(tl, (cc ^ src[i]) & 0xffu);
-                }
-                crc_emit(p, b, p.nfull, ~cc);
+                for (; i + 4 <= left; i += 4) c = step_word(c, *reinterpret_cast<const uint32_t *>(src + i));
+                for (; i < left; i++) c = (c >> 8) ^ lut_lds<0>(tl, (c ^ src[i]) & 0xffu);
+                crc_emit(p, buf, seg, ~c);
             }
+            c = 0xFFFFFFFFu;
         }
     }
 }
@@ -200,74 +216,86 @@ __device__ __forceinline__ uint32_t multmodp_dev(uint32_t a, uint32_t b, uint32_
     return r;
 }
 
-constexpr int COMBINE_MAX_LOG = 10;  // <= 1024 threads per output
-
-struct CombineParams {
-    const uint32_t *partial;           // [n_buf][segs_per_buf] finalised CRCs of seg_bytes-byte segments
-    unsigned long long n_buf, segs_per_buf, outs_per_buf;
-    unsigned int group;                // partials per regular output
-    unsigned int last_cnt;             // partials in the last output of a buffer
-    unsigned int last_has_rag;         // the buffer's final partial covers fewer than seg_bytes bytes
-    uint32_t x_rag;                    // x^(8*rag) mod P
-    uint32_t x1;                       // x^(8*seg_bytes) mod P
-    // regular output: run length R, runs, x^(8*seg_bytes*R)^(2^j), x^(8*seg_bytes*len_of_last_run)
-    unsigned int R_reg, runs_reg;  uint32_t xr_reg[COMBINE_MAX_LOG];  uint32_t xl_reg;
-    unsigned int R_last, runs_last; uint32_t xr_last[COMBINE_MAX_LOG]; uint32_t xl_last;
+// Fold per-segment CRCs into one CRC per output (chunk or whole buffer), one level per launch.
+// Elements are weighted by their distance from the END of the output, counted in elements:
+// element e (0 = last full element) contributes p_e * x^(8*U*e), U = bytes per element. A team of
+// T threads folds T consecutive elements: lane l multiplies by the per-level constant
+// c1[l] = x^(8*U*l), the warp XOR-reduces with shuffles, warp w's value is multiplied by
+// c2[w] = x^(8*U*32*w) and reduced again. Outputs with more than T elements produce one value per
+// block of T, which the next launch folds with U' = U*T. All constants are 32-bit values computed
+// on the host; nothing is irregular: a ragged final element only enters at the last level as
+//   result = fold * x^(8*rag) xor p_rag.
+struct FoldParams {
+    const uint32_t *cur;                // cur[b*cur_stride_buf + oi*cur_group + i], position order
+    unsigned long long n_buf, outs_per_buf, cur_stride_buf;
+    unsigned int cur_group;             // element stride between the outputs of one buffer
+    unsigned int cnt_reg, cnt_last;     // FULL elements in a regular / in the last output of a buffer
+    unsigned int T, nb;                 // team threads; blocks of T elements per output at this level
+    uint32_t c1[32], c2[32];
     uint32_t poly_bits;
-    uint32_t *out;                     // out[b*out_stride + o]
+    int final_level;
+    uint32_t *nxt;                      // !final: nxt[b*nxt_stride_buf + oi*nb + j]
+    unsigned long long nxt_stride_buf;
+    uint32_t x_rag;                     // final: x^(8*rag)
+    int last_has_rag;
+    const uint32_t *rag_src;            // final: level-1 array, ragged element = last of the buffer's last output
+    unsigned long long rag_stride_buf;
+    unsigned int rag_group, rag_last_cnt;
+    uint32_t *out;                      // out[b*out_stride + oi]
     unsigned long long out_stride;
     int big_endian;
     const uint8_t *expect_be;
     unsigned long long *first_bad;
 };
 
-// One CTA per output CRC. Thread t folds a contiguous run of partials by Horner with x1, is
-// shifted to the end of the output with x^(8*seg_bytes*distance), and the CTA XOR-reduces with
-// warp shuffles.
-__global__ void crc_combine_kernel(const __grid_constant__ CombineParams p) {
+__global__ void crc_fold_kernel(const __grid_constant__ FoldParams p) {
     __shared__ uint32_t red[32];
-    const unsigned int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const unsigned int T = p.T, W = T >> 5;
+    const unsigned int tpc = blockDim.x / T;  // teams per CTA
+    const unsigned int team = threadIdx.x / T, tau = threadIdx.x - team * T;
+    const unsigned int lane = tau & 31, wteam = tau >> 5, gwarp = threadIdx.x >> 5;
     const uint32_t P = p.poly_bits;
-    auto run_mult = [&](unsigned int runs, const uint32_t *xr, uint32_t xl) -> uint32_t {
-        if (t + 1 >= runs) return 0x80000000u;  // last run (or idle thread): distance 0
-        unsigned int e = runs - 2 - t;          // full runs between this run and the last one
-        uint32_t m = xl;
-        for (int j = 0; j < COMBINE_MAX_LOG && e; j++, e >>= 1)
-            if (e & 1u) m = multmodp_dev(m, xr[j], P);
-        return m;
-    };
-    const uint32_t mult_reg = run_mult(p.runs_reg, p.xr_reg, p.xl_reg);
-    const unsigned long long total = p.n_buf * p.outs_per_buf;
-    for (unsigned long long o = blockIdx.x; o < total; o += gridDim.x) {
+    const uint32_t my_c1 = p.c1[lane];
+    const uint32_t my_c2 = p.c2[lane];
+    const unsigned long long total = p.n_buf * p.outs_per_buf * p.nb;
+    for (unsigned long long item0 = static_cast<unsigned long long>(blockIdx.x) * tpc; item0 < total;
+         item0 += static_cast<unsigned long long>(gridDim.x) * tpc) {
+        const unsigned long long item = item0 + team;
+        const bool valid = item < total;
+        const unsigned long long o = item / p.nb;
+        const unsigned int blk = static_cast<unsigned int>(item - o * p.nb);
         const unsigned long long b = o / p.outs_per_buf, oi = o - b * p.outs_per_buf;
         const bool is_last = (oi + 1 == p.outs_per_buf);
-        const unsigned int cnt = is_last ? p.last_cnt : p.group;
-        const bool rag = is_last && p.last_has_rag;
-        const unsigned int nreg = cnt - (rag ? 1u : 0u);
-        const unsigned int R = is_last ? p.R_last : p.R_reg;
-        const uint32_t mult = is_last ? run_mult(p.runs_last, p.xr_last, p.xl_last) : mult_reg;
-        const uint32_t *src = p.partial + b * p.segs_per_buf + oi * p.group;
-        const unsigned long long i0 = static_cast<unsigned long long>(t) * R;
-        uint32_t acc = 0;
-        if (i0 < nreg) {
-            const unsigned int i1 = (i0 + R < nreg) ? static_cast<unsigned int>(i0 + R) : nreg;
-            acc = src[i0];
-            for (unsigned int i = static_cast<unsigned int>(i0) + 1; i < i1; i++) acc = multmodp_dev(acc, p.x1, P) ^ src[i];
-            acc = multmodp_dev(acc, mult, P);
-        }
+        const unsigned int cnt = is_last ? p.cnt_last : p.cnt_reg;
+        const unsigned long long e = static_cast<unsigned long long>(blk) * T + tau;
+        const uint32_t *src = p.cur + b * p.cur_stride_buf + oi * p.cur_group;
+        uint32_t v = 0;
+        if (valid && e < cnt) v = multmodp_dev(src[cnt - 1 - e], my_c1, P);
 #pragma unroll
-        for (int s = 16; s > 0; s >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, s);
-        __syncthreads();
-        if (lane == 0) red[warp] = acc;
-        __syncthreads();
-        if (t == 0) {
-            uint32_t r = 0;
-            for (unsigned int w = 0; w < (blockDim.x + 31) / 32; w++) r ^= red[w];
-            if (rag) r = multmodp_dev(r, p.x_rag, P) ^ src[cnt - 1];
-            if (p.out) p.out[b * p.out_stride + oi] = p.big_endian ? bswap32(r) : r;
-            if (p.expect_be) {
-                const uint32_t want = *reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * oi);
-                if (want != bswap32(r)) atomicMin(p.first_bad, oi);
+        for (int s = 16; s > 0; s >>= 1) v ^= __shfl_xor_sync(0xffffffffu, v, s);
+        if (W > 1) {
+            __syncthreads();
+            if (lane == 0) red[gwarp] = v;
+            __syncthreads();
+            if (wteam == 0) {
+                v = (lane < W) ? multmodp_dev(red[team * W + lane], my_c2, P) : 0u;
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) v ^= __shfl_xor_sync(0xffffffffu, v, s);
+            }
+        }
+        if (valid && tau == 0) {
+            const unsigned int nb_o = (cnt + T - 1) / T;
+            if (!p.final_level) {
+                if (blk < nb_o) p.nxt[b * p.nxt_stride_buf + oi * p.nb + (nb_o - 1 - blk)] = v;
+            } else {
+                uint32_t r = v;
+                if (is_last && p.last_has_rag)
+                    r = multmodp_dev(r, p.x_rag, P) ^ p.rag_src[b * p.rag_stride_buf + oi * p.rag_group + p.rag_last_cnt - 1];
+                if (p.out) p.out[b * p.out_stride + oi] = p.big_endian ? bswap32(r) : r;
+                if (p.expect_be) {
+                    const uint32_t want = *reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * oi);
+                    if (want != bswap32(r)) atomicMin(p.first_bad, oi);
+                }
             }
         }
     }

@@ -218,11 +218,9 @@ static void launch_lut8(const RsParams &p, int grid, cudaStream_t st) {
     rs_lut8_kernel<K><<<grid, RS_THREADS, K * 256 * 32 * 4, st>>>(p);
 }
 
-// out slot out_idx[r] = XOR_j rows[r*n_in+j] * in slot in_idx[j]
-static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, const int *in_idx, int n_in,
-                        const int *out_idx, int n_out, cudaStream_t st) {
-    if (n_in <= 0 || n_out <= 0) return GPU_EC_ERR_INVALID_ARG;
-    if (s.n_stripes == 0 || s.shard_len == 0) return GPU_EC_OK;
+// one kernel launch: out slot out_idx[r] (r < no) (^)= XOR_{j<ni} rows[r][j] * in slot in_idx[j]
+static int launch_apply_pass(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, size_t row_stride, const int *in_idx,
+                             int ni, const int *out_idx, int no, bool accumulate, bool use_lut8, cudaStream_t st) {
     RsParams p;
     memset(&p, 0, sizeof p);
     p.base = s.base;
@@ -231,34 +229,75 @@ static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, co
     p.nvec = static_cast<unsigned int>(div_up(s.shard_len, 16));
     p.tiles_per_stripe = static_cast<unsigned int>(div_up(p.nvec, RS_THREADS));
     p.n_tiles = static_cast<unsigned long long>(s.n_stripes) * p.tiles_per_stripe;
+    p.n_in = ni;
+    p.n_out = no;
+    p.accumulate = accumulate ? 1 : 0;
+    for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[r];
+    for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j];
+    for (int r = 0; r < no; r++)
+        for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * row_stride + j];
     const int grid = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count)));
+    if (use_lut8) {
+        switch (ni) {
+            case 1: launch_lut8<1>(p, grid, st); break;
+            case 2: launch_lut8<2>(p, grid, st); break;
+            case 3: launch_lut8<3>(p, grid, st); break;
+            case 4: launch_lut8<4>(p, grid, st); break;
+            case 5: launch_lut8<5>(p, grid, st); break;
+            case 6: launch_lut8<6>(p, grid, st); break;
+            default: launch_lut8<7>(p, grid, st); break;
+        }
+    } else {
+        rs_lut4_kernel<<<grid, RS_THREADS, ni * 4096, st>>>(p);
+    }
+    g_launches++;
+    CK(cudaGetLastError());
+    return GPU_EC_OK;
+}
+
+// out slot out_idx[r] = XOR_j rows[r*n_in+j] * in slot in_idx[j].
+// n_in <= 7 and n_out <= 4: ONE pass of the byte-LUT kernel over everything.
+// Otherwise several passes (output rows in groups of 4; inputs in balanced groups of <= 7 for the
+// byte-LUT kernel, or of <= 56 for the split-nibble kernel when the code is very wide), run block by
+// block: a block is a range of stripes (or of columns of one stripe) whose 4 output rows fit well
+// inside the 126 MB L2, so the partial parity a pass accumulates into is still L2-resident and
+// only the inputs stream from HBM — one lookup per input byte and ~algorithmic HBM traffic.
+static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, const int *in_idx, int n_in,
+                        const int *out_idx, int n_out, cudaStream_t st) {
+    if (n_in <= 0 || n_out <= 0) return GPU_EC_ERR_INVALID_ARG;
+    if (s.n_stripes == 0 || s.shard_len == 0) return GPU_EC_OK;
+    if (n_in <= RS_LUT8_MAX_IN && n_out <= RS_MAX_OUT)
+        return launch_apply_pass(d, s, rows, n_in, in_idx, n_in, out_idx, n_out, false, true, st);
+    static const bool force_lut4 = getenv("GPU_EC_FORCE_LUT4") != nullptr;  // kernel experiments only
+    const bool lut8 = n_in <= 2 * RS_LUT8_MAX_IN && !force_lut4;
+    const int max_in = lut8 ? RS_LUT8_MAX_IN : RS_LUT4_MAX_IN;
+    const int n_groups = static_cast<int>(div_up(n_in, max_in));
+    const int per_group = static_cast<int>(div_up(n_in, n_groups));  // balanced: 10 -> 5 + 5
+    // measured on B200: per-block launches cost more than the L2 hits save (tools/exp_kernels.py), so by
+    // default a pass covers every stripe; GPU_EC_L2_BLOCK_MB re-enables blocking for experiments
+    static const size_t L2_BLOCK = [] { const char *e = getenv("GPU_EC_L2_BLOCK_MB"); return e ? (static_cast<size_t>(atoi(e)) << 20) : ~size_t(0) / 4; }();
+    const size_t tile_bytes = static_cast<size_t>(RS_THREADS) * 16;
     for (int o0 = 0; o0 < n_out; o0 += RS_MAX_OUT) {
         const int no = std::min(RS_MAX_OUT, n_out - o0);
-        p.n_out = no;
-        for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[o0 + r];
-        const int max_in = (n_in <= RS_LUT8_MAX_IN) ? RS_LUT8_MAX_IN : RS_LUT4_MAX_IN;
-        for (int j0 = 0; j0 < n_in; j0 += max_in) {
-            const int ni = std::min(max_in, n_in - j0);
-            p.n_in = ni;
-            p.accumulate = j0 > 0;
-            for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j0 + j];
-            for (int r = 0; r < no; r++)
-                for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(o0 + r) * n_in + j0 + j];
-            if (n_in <= RS_LUT8_MAX_IN) {
-                switch (ni) {
-                    case 1: launch_lut8<1>(p, grid, st); break;
-                    case 2: launch_lut8<2>(p, grid, st); break;
-                    case 3: launch_lut8<3>(p, grid, st); break;
-                    case 4: launch_lut8<4>(p, grid, st); break;
-                    case 5: launch_lut8<5>(p, grid, st); break;
-                    case 6: launch_lut8<6>(p, grid, st); break;
-                    default: launch_lut8<7>(p, grid, st); break;
+        const size_t out_per_stripe = static_cast<size_t>(no) * s.shard_len;
+        const bool split_cols = (n_groups > 1) && out_per_stripe > L2_BLOCK;
+        const size_t stripes_per_block = (n_groups == 1) ? s.n_stripes
+                                         : split_cols     ? 1
+                                                          : std::max<size_t>(1, L2_BLOCK / out_per_stripe);
+        const size_t cols_per_block = split_cols ? std::max(tile_bytes, L2_BLOCK / no / tile_bytes * tile_bytes) : s.shard_len;
+        for (size_t i0 = 0; i0 < s.n_stripes; i0 += stripes_per_block) {
+            for (size_t c0 = 0; c0 < s.shard_len; c0 += cols_per_block) {
+                gpu_ec_stripes blk = s;
+                blk.base = s.base + i0 * s.stripe_stride + c0;
+                blk.n_stripes = std::min(stripes_per_block, s.n_stripes - i0);
+                blk.shard_len = std::min(cols_per_block, s.shard_len - c0);
+                for (int g = 0; g < n_groups; g++) {
+                    const int j0 = g * per_group, ni = std::min(per_group, n_in - j0);
+                    if (ni <= 0) break;
+                    RET(launch_apply_pass(d, blk, rows + static_cast<size_t>(o0) * n_in + j0, n_in, in_idx + j0, ni,
+                                          out_idx + o0, no, g > 0, lut8, st));
                 }
-            } else {
-                rs_lut4_kernel<<<grid, RS_THREADS, ni * 4096, st>>>(p);
             }
-            g_launches++;
-            CK(cudaGetLastError());
         }
     }
     return GPU_EC_OK;
@@ -276,47 +315,89 @@ struct CrcJob {
     unsigned long long *first_bad = nullptr;
 };
 
+// words of second-level scratch launch_combine needs for outputs of up to `maxcnt` full elements
+static size_t fold_scratch_words(size_t n_outputs, size_t maxcnt) {
+    size_t words = 0;
+    while (maxcnt > 1024) {
+        maxcnt = div_up(maxcnt, 1024);
+        words += n_outputs * maxcnt;
+    }
+    return words;
+}
+
+// Fold `segs_per_buf` per-segment CRCs per buffer (seg_bytes each, the buffer's last one maybe
+// shorter) into one CRC per `group` segments. scratch2 (fold_scratch_words) is only touched when
+// an output has more than 1024 segments; pass nullptr to take it from the stream-ordered allocator.
 static int launch_combine(Dev &d, const uint32_t *partial, size_t n_buf, size_t segs_per_buf, size_t seg_bytes,
-                          size_t len, size_t group, const CrcJob &j, cudaStream_t st) {
+                          size_t len, size_t group, const CrcJob &j, cudaStream_t st, uint32_t *scratch2 = nullptr) {
     const uint32_t P = kPolyReflected[j.poly];
-    CombineParams c;
-    memset(&c, 0, sizeof c);
-    c.partial = partial;
-    c.n_buf = n_buf;
-    c.segs_per_buf = segs_per_buf;
-    c.group = static_cast<unsigned int>(group);
-    c.outs_per_buf = div_up(segs_per_buf, group);
-    c.last_cnt = static_cast<unsigned int>(segs_per_buf - (c.outs_per_buf - 1) * group);
+    FoldParams f;
+    memset(&f, 0, sizeof f);
+    f.n_buf = n_buf;
+    f.outs_per_buf = div_up(segs_per_buf, group);
+    const size_t last_cnt = segs_per_buf - (f.outs_per_buf - 1) * group;
     const size_t rag = len % seg_bytes;
-    c.last_has_rag = rag ? 1 : 0;
-    c.x_rag = x8n_modp(rag, P);
-    c.x1 = x8n_modp(seg_bytes, P);
-    c.poly_bits = P;
-    const unsigned int maxcnt = static_cast<unsigned int>(std::max<size_t>(c.group, c.last_cnt));
-    const unsigned int T = static_cast<unsigned int>(std::min<size_t>(1024, round_up(std::min<unsigned int>(maxcnt, 1024u), 32)));
-    auto plan = [&](unsigned int nreg, unsigned int &R, unsigned int &runs, uint32_t *xr, uint32_t &xl) {
-        if (nreg == 0) { R = 1; runs = 0; xl = 0x80000000u; for (int i = 0; i < COMBINE_MAX_LOG; i++) xr[i] = 0x80000000u; return; }
-        R = static_cast<unsigned int>(div_up(nreg, T));
-        runs = static_cast<unsigned int>(div_up(nreg, R));
-        const unsigned int llast = nreg - (runs - 1) * R;
-        xl = x8n_modp(static_cast<uint64_t>(seg_bytes) * llast, P);
-        uint32_t v = x8n_modp(static_cast<uint64_t>(seg_bytes) * R, P);
-        for (int i = 0; i < COMBINE_MAX_LOG; i++) { xr[i] = v; v = multmodp(v, v, P); }
-    };
-    plan(c.group, c.R_reg, c.runs_reg, c.xr_reg, c.xl_reg);
-    plan(c.last_cnt - (c.last_has_rag ? 1u : 0u), c.R_last, c.runs_last, c.xr_last, c.xl_last);
-    c.out = j.out;
-    c.out_stride = j.out_stride;
-    c.big_endian = j.big_endian;
-    c.expect_be = j.expect_be;
-    c.first_bad = j.first_bad;
-    const unsigned long long total = static_cast<unsigned long long>(n_buf) * c.outs_per_buf;
-    const int per_sm = std::max(1, 2048 / static_cast<int>(T));
-    const int grid = static_cast<int>(std::min<unsigned long long>(total, static_cast<unsigned long long>(d.sm_count) * per_sm));
-    crc_combine_kernel<<<grid, T, 0, st>>>(c);
-    g_launches++;
-    CK(cudaGetLastError());
+    f.last_has_rag = rag ? 1 : 0;
+    f.x_rag = x8n_modp(rag, P);
+    f.rag_src = partial; f.rag_stride_buf = segs_per_buf;
+    f.rag_group = static_cast<unsigned int>(group); f.rag_last_cnt = static_cast<unsigned int>(last_cnt);
+    f.poly_bits = P;
+    f.out = j.out; f.out_stride = j.out_stride; f.big_endian = j.big_endian;
+    f.expect_be = j.expect_be; f.first_bad = j.first_bad;
+    size_t cnt_last = last_cnt - (rag ? 1 : 0);
+    size_t cnt_reg = f.outs_per_buf > 1 ? group : cnt_last;
+    const size_t n_outputs = n_buf * f.outs_per_buf;
+    const size_t need2 = fold_scratch_words(n_outputs, std::max(cnt_reg, cnt_last));
+    uint32_t *owned = nullptr;
+    if (need2 && !scratch2) { CK(cudaMallocAsync(&owned, 4 * need2, st)); scratch2 = owned; }
+    f.cur = partial; f.cur_stride_buf = segs_per_buf; f.cur_group = static_cast<unsigned int>(group);
+    uint64_t U = seg_bytes;
+    for (;;) {
+        const size_t maxcnt = std::max(cnt_reg, cnt_last);
+        unsigned int T = 32;
+        while (T < 1024 && T < maxcnt) T <<= 1;
+        f.T = T;
+        f.nb = static_cast<unsigned int>(std::max<size_t>(1, div_up(maxcnt, T)));
+        f.final_level = (f.nb == 1);
+        f.cnt_reg = static_cast<unsigned int>(cnt_reg);
+        f.cnt_last = static_cast<unsigned int>(cnt_last);
+        {   // c1[l] = x^(8*U*l), c2[w] = x^(8*U*32*w): one power, then 62 products
+            const uint32_t xu = x8n_modp(U, P);
+            f.c1[0] = 0x80000000u;
+            for (int l = 1; l < 32; l++) f.c1[l] = multmodp(f.c1[l - 1], xu, P);
+            const uint32_t xu32 = multmodp(f.c1[31], xu, P);
+            f.c2[0] = 0x80000000u;
+            for (int l = 1; l < 32; l++) f.c2[l] = multmodp(f.c2[l - 1], xu32, P);
+        }
+        if (!f.final_level) { f.nxt = scratch2; f.nxt_stride_buf = f.outs_per_buf * f.nb; }
+        const unsigned int block = std::max(T, 256u);
+        const unsigned long long items = static_cast<unsigned long long>(n_outputs) * f.nb;
+        const unsigned long long ctas = div_up(items, block / T);
+        const int grid = static_cast<int>(std::min<unsigned long long>(ctas, static_cast<unsigned long long>(d.sm_count) * (2048 / block) * 4));
+        crc_fold_kernel<<<grid, block, 0, st>>>(f);
+        g_launches++;
+        CK(cudaGetLastError());
+        if (f.final_level) break;
+        f.cur = scratch2; f.cur_stride_buf = f.nxt_stride_buf; f.cur_group = f.nb;
+        scratch2 += n_outputs * f.nb;
+        cnt_reg = div_up(cnt_reg, T); cnt_last = div_up(cnt_last, T);
+        U *= T;
+    }
+    if (owned) CK(cudaFreeAsync(owned, st));
     return GPU_EC_OK;
+}
+
+// whole-buffer mode: segment length that fills an integer number of waves of (SMs x warps) tiles
+static size_t pick_whole_segment(const Dev &d, size_t n_buf, size_t len) {
+    const size_t wave_tiles = static_cast<size_t>(d.sm_count) * CRC_WARPS;
+    const size_t G_CAP = 16384;
+    for (size_t w = 1; w <= 64; w++) {
+        const size_t tpb = w * wave_tiles / n_buf;  // 32-segment tiles each buffer may use
+        if (tpb == 0) continue;
+        const size_t G = round_up(div_up(len, 32 * tpb), 128);
+        if (G <= G_CAP) return std::max<size_t>(G, 512);
+    }
+    return G_CAP;
 }
 
 static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
@@ -336,9 +417,7 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     if (aligned) {
         const unsigned long long total = static_cast<unsigned long long>(j.n_buf) * j.len;
         if (whole) {
-            G = 512;  // most parallelism; longer segments only when there are waves to spare
-            for (size_t g : {size_t(16384), size_t(8192), size_t(4096), size_t(2048), size_t(1024)})
-                if (total / g >= 4 * lanes_wave) { G = g; break; }
+            G = pick_whole_segment(d, j.n_buf, j.len);
         } else if (j.chunk % 128 == 0) {
             if (j.chunk <= 1024) {
                 G = j.chunk;  // one lane per chunk, CRC written directly
@@ -373,25 +452,27 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     p.nfull = j.len / G;
     p.rag = static_cast<unsigned int>(j.len % G);
     p.segs_per_buf = p.nfull + (p.rag ? 1 : 0);
-    p.tiles_per_buf = div_up(p.nfull, 32);
+    p.tiles_per_buf = div_up(p.segs_per_buf, 32);
     p.poly = j.poly;
     const bool direct = !whole && G == j.chunk;
     uint32_t *scratch = nullptr;
+    const size_t group = whole ? static_cast<size_t>(p.segs_per_buf) : j.chunk / G;
+    const size_t n_part = static_cast<size_t>(j.n_buf) * p.segs_per_buf;
     if (direct) {
         p.out = j.out; p.out_stride = j.out_stride; p.big_endian = j.big_endian;
         p.expect_be = j.expect_be; p.first_bad = j.first_bad;
     } else {
-        CK(cudaMallocAsync(&scratch, 4ull * j.n_buf * p.segs_per_buf, st));
+        const size_t need2 = fold_scratch_words(j.n_buf * div_up(p.segs_per_buf, group), group);
+        CK(cudaMallocAsync(&scratch, 4ull * (n_part + need2), st));
         p.out = scratch; p.out_stride = p.segs_per_buf;
     }
-    const unsigned long long warps = j.n_buf * p.tiles_per_buf + (p.rag ? j.n_buf : 0);
+    const unsigned long long warps = j.n_buf * p.tiles_per_buf;
     const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(d.sm_count))));
     crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     g_launches++;
     CK(cudaGetLastError());
     if (!direct) {
-        const size_t group = whole ? p.segs_per_buf : j.chunk / G;
-        int rc = launch_combine(d, scratch, j.n_buf, p.segs_per_buf, G, j.len, group, j, st);
+        int rc = launch_combine(d, scratch, j.n_buf, p.segs_per_buf, G, j.len, group, j, st, scratch + n_part);
         CK(cudaFreeAsync(scratch, st));
         RET(rc);
     }
@@ -671,23 +752,18 @@ int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original
     RET(dev_of_ptr(s->base, &d));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int n = k + m;
-    // stripe groups of <= 64 MiB so the parity just written is checksummed while still in L2
-    const size_t per_stripe = static_cast<size_t>(n) * S;
-    const size_t grp = std::max<size_t>(1, (64ull << 20) / std::max<size_t>(per_stripe, 1));
-    for (size_t i0 = 0; i0 < s->n_stripes; i0 += grp) {
-        const size_t cnt = std::min(grp, s->n_stripes - i0);
-        gpu_ec_stripes sub = *s;
-        sub.base = s->base + i0 * s->stripe_stride;
-        sub.n_stripes = cnt;
-        RET(encode_dev_impl(*d, sub, k, m, st));
+    // encode every stripe, then checksum every shard: two streaming passes. (Per-stripe-group launch
+    // chains that keep the parity L2-warm were measured slower: small launches underfill the GPU.)
+    RET(encode_dev_impl(*d, *s, k, m, st));
+    {
         CrcJob j;
         j.buf_stride = s->shard_stride; j.len = S; j.chunk = 0; j.poly = poly; j.out_stride = 1;
-        if (s->stripe_stride == static_cast<size_t>(n) * s->shard_stride) {  // all shards of the group at one stride
-            j.base = sub.base; j.n_buf = cnt * n; j.out = shard_crc + i0 * n;
+        if (s->stripe_stride == static_cast<size_t>(n) * s->shard_stride) {  // all shards at one stride
+            j.base = s->base; j.n_buf = s->n_stripes * n; j.out = shard_crc;
             RET(launch_crc(*d, j, st));
         } else {
-            for (size_t i = 0; i < cnt; i++) {
-                j.base = sub.base + i * s->stripe_stride; j.n_buf = n; j.out = shard_crc + (i0 + i) * n;
+            for (size_t i = 0; i < s->n_stripes; i++) {
+                j.base = s->base + i * s->stripe_stride; j.n_buf = n; j.out = shard_crc + i * n;
                 RET(launch_crc(*d, j, st));
             }
         }
@@ -837,7 +913,8 @@ static int crc_host_common(const uint8_t *data, size_t len, size_t chunk, int po
     const size_t crc_off = data_cap;
     const size_t whole_off = crc_off + round_up(4 * nchunks, 256);
     const size_t meta_off = whole_off + 256;
-    const size_t need = meta_off + round_up(4 * nchunks, 256) + 256;
+    const size_t fold_off = meta_off + round_up(4 * nchunks, 256) + 256;
+    const size_t need = fold_off + 4 * fold_scratch_words(1, nchunks) + 256;
     Lease L;
     RET(lease_any(L));
     RET(slot_reserve(*L.s, need));
@@ -863,7 +940,7 @@ static int crc_host_common(const uint8_t *data, size_t len, size_t chunk, int po
         if (chunk && nchunks) {  // fold the chunk CRCs: the bytes were read once (chunkserver.rs:746-769 + 195)
             CrcJob j;
             j.poly = poly; j.out = d_whole; j.out_stride = 1;
-            RET(launch_combine(*L.d, d_chunks, 1, nchunks, chunk, len, nchunks, j, st));
+            RET(launch_combine(*L.d, d_chunks, 1, nchunks, chunk, len, nchunks, j, st, reinterpret_cast<uint32_t *>(db + fold_off)));
         } else {
             CrcJob j;
             j.base = db; j.n_buf = 1; j.buf_stride = data_cap; j.len = len; j.chunk = 0; j.poly = poly;
@@ -1135,9 +1212,11 @@ int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_strid
         CK(cudaGetLastError());
         return GPU_EC_OK;
     }
-    // shortest segment (most parallelism) whose partial count fits the fixed array
+    // shortest segment (most parallelism) whose per-segment CRCs, plus the few words the fold needs
+    // beyond 1024 segments per buffer, fit the fixed array
+    auto words_for = [&](size_t g) { const size_t segs = div_up(len, g); return n_buf * segs + fold_scratch_words(n_buf, segs); };
     size_t G = 512;
-    while (G <= NOALLOC_MAX_SEGMENT && n_buf * div_up(len, G) > NOALLOC_MAX_PARTIALS) G *= 2;
+    while (G <= NOALLOC_MAX_SEGMENT && words_for(G) > NOALLOC_MAX_PARTIALS) G *= 2;
     if (G > NOALLOC_MAX_SEGMENT) {
         char msg[256];
         snprintf(msg, sizeof msg,
@@ -1154,16 +1233,17 @@ int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_strid
     p.nfull = len / G;
     p.rag = static_cast<unsigned int>(len % G);
     p.segs_per_buf = p.nfull + (p.rag ? 1 : 0);
-    p.tiles_per_buf = div_up(p.nfull, 32);
+    p.tiles_per_buf = div_up(p.segs_per_buf, 32);
     p.poly = poly;
     p.out = nd->scratch;  // the device address, never the host-side symbol
     p.out_stride = p.segs_per_buf;
-    const unsigned long long warps = n_buf * p.tiles_per_buf + (p.rag ? n_buf : 0);
+    const unsigned long long warps = n_buf * p.tiles_per_buf;
     const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(sms))));
     crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     g_launches++;
     CK(cudaGetLastError());
-    return launch_combine(nd->shim, nd->scratch, n_buf, p.segs_per_buf, G, len, p.segs_per_buf, j, st);
+    return launch_combine(nd->shim, nd->scratch, n_buf, p.segs_per_buf, G, len, p.segs_per_buf, j, st,
+                          nd->scratch + n_buf * p.segs_per_buf);
 }
 
 }  // extern "C"

@@ -48,24 +48,22 @@ struct RsParams {
     uint8_t coef[RS_MAX_OUT][RS_LUT4_MAX_IN];
 };
 
-__device__ __forceinline__ uint32_t gf_mul_dev(uint32_t a, uint32_t b) {
-    uint32_t r = 0;
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-        r ^= (b & 1u) ? a : 0u;
-        a <<= 1;
-        a ^= (a & 0x100u) ? 0x11Du : 0u;
-        b >>= 1;
-    }
-    return r & 0xffu;
-}
-
-// packed products of byte value `x` with the coefficients of input column j for all output rows
+// packed products of byte value `x` with the coefficients of input column j for all output rows:
+// the four coefficients sit in the four bytes of one word and are doubled together (packed
+// multiply-by-x in GF(2^8), polynomial 0x11D), so one Russian-peasant loop yields all four products
 __device__ __forceinline__ uint32_t packed_products(const RsParams &p, int j, uint32_t x) {
-    uint32_t v = 0;
+    uint32_t c = 0;
 #pragma unroll
     for (int r = 0; r < RS_MAX_OUT; r++)
-        if (r < p.n_out) v |= gf_mul_dev(p.coef[r][j], x) << (8 * r);
+        if (r < p.n_out) c |= static_cast<uint32_t>(p.coef[r][j]) << (8 * r);
+    uint32_t v = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        v ^= ((x >> i) & 1u) ? c : 0u;
+        uint32_t hi;  // 0xFF in every byte whose top bit is set (prmt with sign-replicate selectors)
+        asm("prmt.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(c), "r"(0u), "r"(0xBA98u));
+        c = ((c & 0x7f7f7f7fu) << 1) ^ (hi & 0x1d1d1d1du);
+    }
     return v;
 }
 

@@ -9,7 +9,7 @@ import os
 import subprocess
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SO_PATH = os.path.join(_PKG, "libgpu_ec.so")
+SO_PATH = os.environ.get("GPU_EC_LIB") or os.path.join(_PKG, "libgpu_ec.so")  # override: kernel experiments only
 CSRC = os.path.join(_PKG, "csrc")
 
 OK = 0

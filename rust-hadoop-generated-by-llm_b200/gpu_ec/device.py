@@ -36,20 +36,19 @@ class StripeBatch:
         return Stripes(self.buf.data_ptr() + first * stripe_stride, self.pitch, stripe_stride, self.shard_len, count)
 
     def fill_synthetic(self, seed: int, original_len: int = 0) -> None:
-        """Data slots [0,k) of stripe i get synthetic bytes; the stream position of slot j of stripe i
-        is (i*k + j) * pitch so any rank / the oracle can regenerate any shard independently.
-        With original_len < k*shard_len the tail is zeroed like erasure.rs:18 pads it."""
-        L = lib()
-        st = _stream_ptr()
-        for i in range(self.n_stripes):
-            for j in range(self.k):
-                off = (i * self.k + j) * self.pitch
-                check(L.gpu_ec_fill_synthetic_dev(self.buf[i, j].data_ptr(), self.shard_len, seed, off, st))
+        """One launch fills the whole pitched buffer with the synthetic stream (slot s of stripe i
+        starts at stream position (i*(k+m) + s) * pitch, so the oracle can regenerate any shard
+        independently); parity slots are overwritten by encode. With original_len < k*shard_len
+        the tail of the data slots is zeroed like erasure.rs:18 pads it."""
+        check(lib().gpu_ec_fill_synthetic_dev(self.buf.data_ptr(), self.buf.numel(), seed, 0, _stream_ptr()))
         if original_len and original_len < self.k * self.shard_len:
             for j in range(self.k):
                 keep = min(max(original_len - j * self.shard_len, 0), self.shard_len)
                 if keep < self.shard_len:
                     self.buf[:, j, keep:self.shard_len] = 0
+
+    def stream_offset(self, i: int, s: int) -> int:
+        return (i * (self.k + self.m) + s) * self.pitch
 
     def shard_host(self, i: int, s: int) -> np.ndarray:
         return self.buf[i, s, :self.shard_len].cpu().numpy()

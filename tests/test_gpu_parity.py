@@ -323,7 +323,7 @@ def test_dev_encode_reconstruct_crc(L, orc, k, m, stripe_len, n_stripes):
     b.fill_synthetic(0xEC0000AA, original_len=stripe_len)
     torch.cuda.synchronize()
     data0 = [b.shard_host(0, j) for j in range(k)]
-    assert np.array_equal(data0[1], orc.fill_synthetic(S, 0xEC0000AA, 1 * b.pitch))
+    assert np.array_equal(data0[1], orc.fill_synthetic(S, 0xEC0000AA, b.stream_offset(0, 1)))
     shard_crc, full = b.encode_crc(original_len=stripe_len)
     torch.cuda.synchronize()
     shard_crc, full = device.u32(shard_crc), device.u32(full)
@@ -383,7 +383,7 @@ def test_linearity_and_checksum_of_checksums_full_size(L):
     c = device.StripeBatch(1, k, m, S)
     c.buf[0, :k] = x
     c.encode()
-    assert torch.equal(c.buf[0, k:], a.buf[0, k:] ^ a.buf[1, k:])  # encode(a^b) == encode(a)^encode(b)
+    assert torch.equal(c.buf[0, k:, :S], (a.buf[0, k:] ^ a.buf[1, k:])[:, :S])  # encode(a^b) == encode(a)^encode(b)
     # erase -> reconstruct round trip at full size
     ref = a.buf.clone()
     a.buf[:, 0] = 0

@@ -1,0 +1,79 @@
+#!/usr/bin/env python3
+"""Kernel experiments (not part of the product): time individual device-resident launches.
+usage: python tools/exp_kernels.py crc|rs104|rs63 ..."""
+import ctypes as C
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "rust-hadoop-generated-by-llm_b200"))
+import numpy as np
+import torch
+import gpu_ec
+from gpu_ec import device
+from gpu_ec._lib import check
+
+L = gpu_ec.lib()
+PEAK = 6557.8
+
+
+def timed(fn, steps=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def crc():
+    n = 1 << 30
+    t = torch.empty(n, dtype=torch.uint8, device="cuda")
+    device.fill_synthetic(t, 2)
+    for chunk in (512, 65536):
+        out = torch.empty(n // chunk, dtype=torch.int32, device="cuda")
+        ms = timed(lambda: device.crc32_chunks(t, chunk, out=out))
+        print(f"crc chunk={chunk}: {n/ms/1e6:.0f} GB/s frac={n/ms/1e6/PEAK:.3f}")
+    # whole-buffer CRC of 14 shards of a 64 MiB RS(10,4) stripe (one fused-path group)
+    S, pitch = 6710887, 6711040
+    o = torch.empty(14, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    ms = timed(lambda: check(L.gpu_ec_crc32_dev(t.data_ptr(), 14, pitch, S, 0, o.data_ptr(), st)), 20)
+    print(f"crc whole 14x6.7MB: {ms*1e3:.1f} us  {14*S/ms/1e6:.0f} GB/s")
+    ms = timed(lambda: check(L.gpu_ec_crc32_dev(t.data_ptr(), 140, pitch, S, 0, torch.empty(140, dtype=torch.int32, device='cuda').data_ptr(), st)), 10)
+    print(f"crc whole 140x6.7MB: {ms*1e3:.1f} us  {140*S/ms/1e6:.0f} GB/s")
+
+
+def rs(k, m, stripe_len, n):
+    S = gpu_ec.erasure.shard_len(stripe_len, k)
+    b = device.StripeBatch(n, k, m, S)
+    b.fill_synthetic(4)
+    ms = timed(b.encode, 5)
+    a = (k + m) * S * n
+    print(f"rs({k},{m}) n={n} L2_BLOCK_MB={os.environ.get('GPU_EC_L2_BLOCK_MB')} lut4={os.environ.get('GPU_EC_FORCE_LUT4')}: "
+          f"{ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
+    if k == 10:
+        # single pass of 5 inputs -> 4 outputs over everything (how fast is one byte-LUT pass?)
+        M = gpu_ec.erasure.coding_matrix(k, m)
+        rows = np.ascontiguousarray(M[k:, :5])
+        ii = (C.c_int * 5)(0, 1, 2, 3, 4)
+        oo = (C.c_int * 4)(10, 11, 12, 13)
+        d = b.desc()
+        st = torch.cuda.current_stream().cuda_stream
+        ms = timed(lambda: check(L.gpu_ec_apply_matrix_dev(C.byref(d), rows.ctypes.data, ii, 5, oo, 4, st)), 5)
+        a1 = 9 * S * n
+        print(f"   one lut8<5> pass (5 in, 4 out) over all stripes: {ms:.3f} ms {a1/ms/1e6:.0f} GB/s (bytes moved)")
+
+
+if __name__ == "__main__":
+    what = sys.argv[1]
+    if what == "crc":
+        crc()
+    elif what == "rs104":
+        rs(10, 4, 64 << 20, 48)
+    elif what == "rs63":
+        rs(6, 3, 64 << 20, 64)
