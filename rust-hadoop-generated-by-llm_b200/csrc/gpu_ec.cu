@@ -70,6 +70,8 @@ struct Ctx {
 };
 static Ctx &ctx() { static Ctx c; return c; }
 
+static constexpr int x2_smem_bytes(int kh) { return kh * 256 * 32 * 4 + RS_X2_XBUF_BYTES + RS_X2_MBAR_BYTES; }
+
 template <int K>
 static int set_lut8_attr() {
     CK(cudaFuncSetAttribute(rs_lut8_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 256 * 32 * 4));
@@ -94,6 +96,9 @@ static int dev_prepare(Dev &d) {
     RET(set_lut8_attr<1>()); RET(set_lut8_attr<2>()); RET(set_lut8_attr<3>()); RET(set_lut8_attr<4>());
     RET(set_lut8_attr<5>()); RET(set_lut8_attr<6>()); RET(set_lut8_attr<7>());
     CK(cudaFuncSetAttribute(rs_lut4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RS_LUT4_MAX_IN * 4096));
+    CK(cudaFuncSetAttribute(rs_lut8x2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(4)));
+    CK(cudaFuncSetAttribute(rs_lut8x2_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(5)));
+    CK(cudaFuncSetAttribute(rs_lut8x2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(6)));
     CK(cudaFuncSetAttribute(crc_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
     for (auto &s : d.slots) CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     // keep stream-ordered scratch cached instead of returning it to the OS after every call
@@ -255,6 +260,45 @@ static int launch_apply_pass(Dev &d, const gpu_ec_stripes &s, const uint8_t *row
     return GPU_EC_OK;
 }
 
+template <int KH>
+static cudaError_t launch_x2(const RsParams &p, int n_clusters, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * n_clusters);
+    cfg.blockDim = dim3(RS_THREADS);
+    cfg.dynamicSmemBytes = x2_smem_bytes(KH);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, rs_lut8x2_kernel<KH>, p);
+}
+
+static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, size_t row_stride, const int *in_idx,
+                           int ni, const int *out_idx, int no, cudaStream_t st) {
+    RsParams p;
+    memset(&p, 0, sizeof p);
+    p.base = s.base;
+    p.shard_stride = s.shard_stride;
+    p.stripe_stride = s.stripe_stride;
+    p.nvec = static_cast<unsigned int>(div_up(s.shard_len, 16));
+    p.tiles_per_stripe = static_cast<unsigned int>(div_up(p.nvec, RS_THREADS));
+    p.n_tiles = static_cast<unsigned long long>(s.n_stripes) * p.tiles_per_stripe;
+    p.n_in = ni;
+    p.n_out = no;
+    for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[r];
+    for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j];
+    for (int r = 0; r < no; r++)
+        for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * row_stride + j];
+    const int n_clusters = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count / 2)));
+    const int kh = (ni + 1) / 2;
+    cudaError_t e = kh <= 4 ? launch_x2<4>(p, n_clusters, st) : kh == 5 ? launch_x2<5>(p, n_clusters, st) : launch_x2<6>(p, n_clusters, st);
+    g_launches++;
+    CK(e);
+    return GPU_EC_OK;
+}
+
 // out slot out_idx[r] = XOR_j rows[r*n_in+j] * in slot in_idx[j].
 // n_in <= 7 and n_out <= 4: ONE pass of the byte-LUT kernel over everything.
 // Otherwise several passes (output rows in groups of 4; inputs in balanced groups of <= 7 for the
@@ -268,6 +312,14 @@ static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, co
     if (s.n_stripes == 0 || s.shard_len == 0) return GPU_EC_OK;
     if (n_in <= RS_LUT8_MAX_IN && n_out <= RS_MAX_OUT)
         return launch_apply_pass(d, s, rows, n_in, in_idx, n_in, out_idx, n_out, false, true, st);
+    static const bool no_cluster = getenv("GPU_EC_NO_CLUSTER") != nullptr;  // kernel experiments only
+    if (n_in <= 2 * RS_X2_MAX_KH && !no_cluster) {
+        // 8..12 inputs: one pass on 2-CTA clusters (tables split over the SM pair, DSMEM exchange)
+        for (int o0 = 0; o0 < n_out; o0 += RS_MAX_OUT)
+            RET(launch_apply_x2(d, s, rows + static_cast<size_t>(o0) * n_in, n_in, in_idx, n_in, out_idx + o0,
+                                std::min(RS_MAX_OUT, n_out - o0), st));
+        return GPU_EC_OK;
+    }
     static const bool force_lut4 = getenv("GPU_EC_FORCE_LUT4") != nullptr;  // kernel experiments only
     const bool lut8 = n_in <= 2 * RS_LUT8_MAX_IN && !force_lut4;
     const int max_in = lut8 ? RS_LUT8_MAX_IN : RS_LUT4_MAX_IN;

@@ -169,6 +169,191 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
 }
 
 // ---------------------------------------------------------------------------------------------
+// rs_lut8x2: the byte-LUT kernel for 8 <= n_in <= 12 on a thread-block CLUSTER of two CTAs.
+// One SM cannot hold more than 7 lane-replicated 32 KiB tables, so the two SMs of a cluster split
+// the input shards: CTA r owns the tables of inputs [r*KH, r*KH + ni_r), both CTAs walk the same
+// tile sequence, each computes the partial products of ALL output rows from its own inputs (still
+// one lookup per input byte), and they trade halves through distributed shared memory: CTA 0
+// finishes rows [0, h0), CTA 1 rows [h0, n_out); the rows a CTA does not own are sent into its
+// partner's exchange buffer, the rows it owns wait in registers.
+// The hand-over is warp-to-warp and fence-free: warp w of the producer writes only the slots warp
+// w of the consumer reads, with st.async (remote store that completes a transaction count on the
+// consumer's mbarrier full[stage][w]); the consumer's warp waits on that mbarrier one tile later
+// (so the DSMEM latency hides behind a tile of lookups) and hands the slot back with a remote
+// arrive on the producer's empty[stage][w]. No cluster-wide barrier and no memory fence in the loop
+// (a barrier.cluster.arrive.release per tile was measured: its MEMBAR drains the prefetched loads
+// and halves throughput). HBM traffic stays algorithmic: every input byte read once, every output
+// byte written once; DSMEM carries ~0.4 B per input byte.
+constexpr int RS_X2_MAX_KH = 6;  // 6 * 32 KiB tables + 32 KiB exchange + mbarriers <= 227 KiB
+constexpr int RS_X2_NW = RS_THREADS / 32;
+constexpr int RS_X2_XBUF_BYTES = 2 * 2 * RS_THREADS * 16;      // [2 stages][2 rows][RS_THREADS] uint4
+constexpr int RS_X2_MBAR_BYTES = 2 * 2 * RS_X2_NW * 8;         // full[2][NW], empty[2][NW]
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_peer(uint32_t local_smem_addr, uint32_t peer) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(peer));
+    return r;
+}
+// remote 16-byte store that signals 16 bytes of transaction completion on the remote mbarrier
+__device__ __forceinline__ void st_async_peer(uint32_t addr, const uint4 &v, uint32_t mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(addr),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t a, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t a, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_peer(uint32_t remote) { asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory"); }
+__device__ __forceinline__ void mbar_wait(uint32_t a, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(a),
+        "r"(parity)
+        : "memory");
+}
+
+template <int KH>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lut8x2_kernel(const __grid_constant__ RsParams p) {
+    extern __shared__ __align__(16) uint32_t rs_tab[];  // tables | exchange buffer | mbarriers
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    constexpr int NW = RS_X2_NW;
+    const uint32_t rank = cluster_ctarank();
+    const int j_base = static_cast<int>(rank) * KH;
+    const int ni = (p.n_in - j_base < KH) ? (p.n_in - j_base) : KH;  // rank 1 may own one input fewer
+    const int h0 = (p.n_out + 1) >> 1;                               // rows [0,h0) finish on rank 0
+    const int own0 = rank ? h0 : 0, n_own = rank ? (p.n_out - h0) : h0;
+    const int oth0 = rank ? 0 : h0, n_oth = rank ? h0 : (p.n_out - h0);
+
+    for (int e0 = warp * 32; e0 < KH * 256; e0 += NW * 32) {
+        const int e = e0 + lane;
+        const int j = e >> 8;
+        const uint32_t v = (j < ni) ? packed_products(p, j_base + j, static_cast<uint32_t>(e & 255)) : 0u;
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) rs_tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+    }
+    uint4 *xbuf = reinterpret_cast<uint4 *>(rs_tab + KH * 256 * 32);
+    const uint32_t xbuf_s = static_cast<uint32_t>(__cvta_generic_to_shared(xbuf));
+    const uint32_t mbar_s = xbuf_s + RS_X2_XBUF_BYTES;  // full[stage][w] at +(stage*NW+w)*8, empty at +(2*NW + stage*NW+w)*8
+    if (threadIdx.x < 4 * NW) mbar_init(mbar_s + threadIdx.x * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    cluster_sync_all();  // both CTAs resident, tables built, mbarriers initialised before any remote access
+    const uint32_t xbuf_peer = map_to_peer(xbuf_s, rank ^ 1u);
+    const uint32_t mbar_peer = map_to_peer(mbar_s, rank ^ 1u);
+    const uint32_t my_full = mbar_s + warp * 8, my_empty = mbar_s + (2 * NW + warp) * 8;          // + stage*NW*8
+    const uint32_t peer_full = mbar_peer + warp * 8, peer_empty = mbar_peer + (2 * NW + warp) * 8;
+
+    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab)) + lane * 4;
+    const unsigned long long n_clusters = gridDim.x >> 1;
+    unsigned long long t = blockIdx.x >> 1;
+
+    uint4 cur[KH];
+    auto locate = [&](unsigned long long tile, unsigned long long &off) -> bool {
+        const unsigned long long stripe = tile / p.tiles_per_stripe;
+        const unsigned int tt = static_cast<unsigned int>(tile - stripe * p.tiles_per_stripe);
+        const unsigned int v = tt * RS_THREADS + threadIdx.x;
+        off = stripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+        return v < p.nvec;
+    };
+    auto load = [&](uint4 (&d)[KH], unsigned long long off, bool ok) {
+#pragma unroll
+        for (int j = 0; j < KH; j++)
+            d[j] = (ok && j < ni) ? ld_vec(p.base + off + static_cast<unsigned long long>(p.in_idx[j_base + j]) * p.shard_stride)
+                                  : make_uint4(0, 0, 0, 0);
+    };
+    unsigned long long cur_off = 0;
+    bool cur_ok = false;
+    if (t < p.n_tiles) { cur_ok = locate(t, cur_off); load(cur, cur_off, cur_ok); }
+
+    uint4 keep0 = make_uint4(0, 0, 0, 0), keep1 = keep0;  // the rows this CTA owns, from the previous tile
+    unsigned long long keep_off = 0;
+    bool keep_ok = false, have_prev = false;
+    unsigned int it = 0;
+    // finish tile `it-1` (stage (it-1)&1, use (it-1)>>1): wait for the partner's rows, fold, store, free the slot
+#define RS_X2_FINISH_PREV()                                                                                          \
+    do {                                                                                                             \
+        const unsigned int ps_ = (it - 1) & 1u, pu_ = (it - 1) >> 1;                                                 \
+        if (n_own > 0) {                                                                                             \
+            mbar_wait(my_full + ps_ * (NW * 8), pu_ & 1u);                                                           \
+            const uint4 *x = xbuf + ps_ * (2 * RS_THREADS) + threadIdx.x;                                            \
+            uint4 o0_ = x[0], o1_ = make_uint4(0, 0, 0, 0);                                                          \
+            if (n_own > 1) o1_ = x[RS_THREADS];                                                                      \
+            o0_.x ^= keep0.x; o0_.y ^= keep0.y; o0_.z ^= keep0.z; o0_.w ^= keep0.w;                                  \
+            o1_.x ^= keep1.x; o1_.y ^= keep1.y; o1_.z ^= keep1.z; o1_.w ^= keep1.w;                                  \
+            __syncwarp();                                                                                            \
+            if (lane == 0) mbar_arrive_peer(peer_empty + ps_ * (NW * 8)); /* slot may be overwritten */              \
+            if (keep_ok) {                                                                                           \
+                *reinterpret_cast<uint4 *>(p.base + keep_off + static_cast<unsigned long long>(p.out_idx[own0]) * p.shard_stride) = o0_; \
+                if (n_own > 1)                                                                                       \
+                    *reinterpret_cast<uint4 *>(p.base + keep_off + static_cast<unsigned long long>(p.out_idx[own0 + 1]) * p.shard_stride) = o1_; \
+            }                                                                                                        \
+        }                                                                                                            \
+    } while (0)
+
+    for (; t < p.n_tiles; t += n_clusters, it++) {
+        uint4 nxt[KH];
+        unsigned long long nxt_off = 0;
+        bool nxt_ok = false;
+        if (t + n_clusters < p.n_tiles) nxt_ok = locate(t + n_clusters, nxt_off);
+        load(nxt, nxt_off, nxt_ok);
+
+        uint32_t acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) acc[i] = 0;
+#pragma unroll
+        for (int j = 0; j < KH; j++) {
+            const uint32_t tj = tl + j * (256 * 32 * 4);
+            const uint32_t w[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
+                acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
+                acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
+                acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
+            }
+        }
+        uint32_t o[4][4];  // o[q][row]
+#pragma unroll
+        for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
+
+        if (have_prev) RS_X2_FINISH_PREV();  // the partner sent these a whole tile of work ago
+
+        const unsigned int st_ = it & 1u, use_ = it >> 1;
+        if (n_own > 0 && lane == 0) mbar_expect_tx(my_full + st_ * (NW * 8), static_cast<uint32_t>(n_own) * 32u * 16u);
+        if (n_oth > 0) {
+            // the partner's warp must have drained this stage's previous use (first use passes at once)
+            mbar_wait(my_empty + st_ * (NW * 8), (use_ & 1u) ^ 1u);
+        }
+        // rows the partner finishes go into its exchange buffer, rows we finish wait in registers
+        const uint32_t dst = xbuf_peer + (st_ * (2 * RS_THREADS) + threadIdx.x) * 16u;
+        const uint32_t sig = peer_full + st_ * (NW * 8);
+#pragma unroll
+        for (int row = 0; row < RS_MAX_OUT; row++) {
+            const uint4 v = make_uint4(o[0][row], o[1][row], o[2][row], o[3][row]);
+            if (n_oth > 0 && row == oth0) st_async_peer(dst, v, sig);
+            if (n_oth > 1 && row == oth0 + 1) st_async_peer(dst + RS_THREADS * 16, v, sig);
+            if (n_own > 0 && row == own0) keep0 = v;
+            if (n_own > 1 && row == own0 + 1) keep1 = v;
+        }
+        keep_off = cur_off;
+        keep_ok = cur_ok;
+        have_prev = true;
+
+#pragma unroll
+        for (int j = 0; j < KH; j++) cur[j] = nxt[j];
+        cur_ok = nxt_ok;
+        cur_off = nxt_off;
+    }
+    if (have_prev) RS_X2_FINISH_PREV();
+#undef RS_X2_FINISH_PREV
+    cluster_sync_all();  // neither CTA may retire while its partner can still write into it or signal it
+}
+
+// ---------------------------------------------------------------------------------------------
 // rs_lut4: split-nibble packed LUTs, lane-replicated, any n_in <= 56 per pass.
 // smem word index: ((j*2 + half)*16 + nibble)*32 + lane. Two LDS per input byte.
 __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut4_kernel(const __grid_constant__ RsParams p) {

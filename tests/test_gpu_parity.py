@@ -74,10 +74,11 @@ def test_encode_sizes_vs_oracle(L, orc, k, m):
             assert np.array_equal(got[i], want[i]), (k, m, n, i)
 
 
-@pytest.mark.parametrize("k,m", [(12, 4), (8, 8), (20, 6), (56, 4), (60, 10), (100, 28), (250, 6)])
+@pytest.mark.parametrize("k,m", [(12, 4), (8, 8), (9, 3), (11, 2), (13, 3), (14, 2), (20, 6), (56, 4), (60, 10), (100, 28), (250, 6)])
 def test_encode_wide_codes_vs_oracle(L, orc, k, m):
-    # k > 7 takes the split-nibble kernel, m > 4 several output passes, k > 56 accumulate passes
-    for n in [k * 3 + 1, 50_000]:
+    # 8 <= k <= 12: 2-CTA cluster kernel (odd k: uneven split); 13, 14: two byte-LUT passes;
+    # beyond: split-nibble kernel; m > 4: several output passes; k > 56: accumulate passes
+    for n in [k * 3 + 1, 50_000, 3_000_017]:
         data = rnd(n, k * 1000 + m)
         want = orc.encode(data, k, m)
         got = erasure.encode(data, k, m)
