@@ -320,25 +320,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
 #pragma unroll
         for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
 
-        if (have_prev) RS_X2_FINISH_PREV();  // the partner sent these a whole tile of work ago
-
+        // send first (the partner gets its rows as early as possible), then finish the previous tile
         const unsigned int st_ = it & 1u, use_ = it >> 1;
         if (n_own > 0 && lane == 0) mbar_expect_tx(my_full + st_ * (NW * 8), static_cast<uint32_t>(n_own) * 32u * 16u);
-        if (n_oth > 0) {
-            // the partner's warp must have drained this stage's previous use (first use passes at once)
-            mbar_wait(my_empty + st_ * (NW * 8), (use_ & 1u) ^ 1u);
-        }
+        // the partner's warp must have drained this stage's previous use (first use passes at once)
+        if (n_oth > 0) mbar_wait(my_empty + st_ * (NW * 8), (use_ & 1u) ^ 1u);
         // rows the partner finishes go into its exchange buffer, rows we finish wait in registers
         const uint32_t dst = xbuf_peer + (st_ * (2 * RS_THREADS) + threadIdx.x) * 16u;
         const uint32_t sig = peer_full + st_ * (NW * 8);
+        uint4 own_a, own_b;
+        if (p.n_out == RS_MAX_OUT) {  // the common 4-row case: rows are compile-time per rank
+            const uint4 r0 = make_uint4(o[0][0], o[1][0], o[2][0], o[3][0]), r1 = make_uint4(o[0][1], o[1][1], o[2][1], o[3][1]);
+            const uint4 r2 = make_uint4(o[0][2], o[1][2], o[2][2], o[3][2]), r3 = make_uint4(o[0][3], o[1][3], o[2][3], o[3][3]);
+            const bool hi = rank != 0;
+            st_async_peer(dst, hi ? r0 : r2, sig);
+            st_async_peer(dst + RS_THREADS * 16, hi ? r1 : r3, sig);
+            own_a = hi ? r2 : r0;
+            own_b = hi ? r3 : r1;
+        } else {
+            own_a = own_b = make_uint4(0, 0, 0, 0);
 #pragma unroll
-        for (int row = 0; row < RS_MAX_OUT; row++) {
-            const uint4 v = make_uint4(o[0][row], o[1][row], o[2][row], o[3][row]);
-            if (n_oth > 0 && row == oth0) st_async_peer(dst, v, sig);
-            if (n_oth > 1 && row == oth0 + 1) st_async_peer(dst + RS_THREADS * 16, v, sig);
-            if (n_own > 0 && row == own0) keep0 = v;
-            if (n_own > 1 && row == own0 + 1) keep1 = v;
+            for (int row = 0; row < RS_MAX_OUT; row++) {
+                const uint4 v = make_uint4(o[0][row], o[1][row], o[2][row], o[3][row]);
+                if (n_oth > 0 && row == oth0) st_async_peer(dst, v, sig);
+                if (n_oth > 1 && row == oth0 + 1) st_async_peer(dst + RS_THREADS * 16, v, sig);
+                if (n_own > 0 && row == own0) own_a = v;
+                if (n_own > 1 && row == own0 + 1) own_b = v;
+            }
         }
+        if (have_prev) RS_X2_FINISH_PREV();  // the partner sent these a whole tile of work ago
+        keep0 = own_a;
+        keep1 = own_b;
         keep_off = cur_off;
         keep_ok = cur_ok;
         have_prev = true;
