@@ -174,7 +174,9 @@ def main():
     warmup = max(3, args.warmup)
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # bookkeeping only (barrier, max elapsed): stripes are independent, so the data path has no
+        # collective and NCCL/NVLink stay unused by design; gloo keeps stdout to the one JSON line
+        dist.init_process_group("gloo")
     L = gpu_ec.lib()
     devs = (C.c_int * 1)(local)
     check(L.gpu_ec_set_devices(devs, 1))
