@@ -78,7 +78,8 @@ uint32_t gpu_ec_crc32_combine(uint32_t crc1, uint32_t crc2, size_t len2, int pol
 /* erasure.rs:7-24 encode(), fused with the client's per-shard and whole-buffer CRCs
  * (client/src/mod.rs:326-341, 600-611) and the chunkserver's per-512-byte .meta arrays
  * (chunkserver.rs:182-196) when the optional outputs are non-NULL.
- *   shards_out[k+m]  : each shard_len bytes; [0,k) receive the zero-padded input split, [k,k+m) parity
+ *   shards_out[k+m]  : each shard_len bytes; [0,k) receive the zero-padded input split (a NULL entry
+ *                      skips that host copy: the shard is data[j*shard_len..] verbatim), [k,k+m) parity
  *   shard_crc_out    : NULL or k+m words, CRC-32 of each shard
  *   full_crc_out     : NULL or 1 word, CRC-32 of the original `len` bytes
  *   meta_out[k+m]    : NULL or, per shard, 4*ceil(shard_len/512) bytes of big-endian chunk CRCs */

@@ -902,7 +902,7 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
     }
     // systematic data shards are the padded input verbatim (erasure.rs:17-19): host copy while the GPU works
     for (int j = 0; j < k; j++) {
-        if (!shards_out[j]) return GPU_EC_ERR_INVALID_ARG;
+        if (!shards_out[j]) continue;  // caller keeps its own view of the systematic shards
         const size_t off = static_cast<size_t>(j) * S;
         const size_t have = off < len ? std::min(S, len - off) : 0;
         if (have) memcpy(shards_out[j], data + off, have);
