@@ -122,6 +122,15 @@ int gpu_ec_encode_batch(const uint8_t *data, size_t stripe_len, size_t n_stripes
 int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t shard_len,
                              size_t n_stripes, int k, int m);
 
+/* run_background_scrubber (chunkserver.rs:642-718) as one batched call: verify n_blocks blocks of
+ * different sizes against their .meta bytes, pipelined over streams (and devices). Per block i:
+ * status_out[i] = GPU_EC_OK | GPU_EC_ERR_COUNT_MISMATCH | GPU_EC_ERR_CRC_MISMATCH and, when
+ * first_bad_out is non-NULL, first_bad_out[i] = first differing chunk or -1 — the same verdicts
+ * verify_block gives block by block. The return value reports call-level failures only. */
+int gpu_ec_verify_chunks_batch(size_t n_blocks, const uint8_t *const *data, const size_t *lens, size_t chunk,
+                               int poly, const uint8_t *const *meta_be, const size_t *meta_lens,
+                               int *status_out, int64_t *first_bad_out);
+
 /* ---- device-resident entry points (device pointers, stream = cudaStream_t) --------------- */
 /* n_stripes stripes of k+m shard slots in device memory:
  * slot s of stripe i starts at base + i*stripe_stride + s*shard_stride and holds shard_len bytes.

@@ -1161,6 +1161,53 @@ int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t sha
 }
 
 
+int gpu_ec_verify_chunks_batch(size_t n_blocks, const uint8_t *const *data, const size_t *lens, size_t chunk, int poly,
+                               const uint8_t *const *meta_be, const size_t *meta_lens, int *status_out,
+                               int64_t *first_bad_out) {
+    if ((n_blocks && (!data || !lens || !meta_be || !meta_lens || !status_out)) || chunk == 0 || (poly != 0 && poly != 1))
+        return GPU_EC_ERR_INVALID_ARG;
+    if (n_blocks == 0) return GPU_EC_OK;
+    BatchLanes B;
+    RET(B.acquire(3));
+    const size_t lanes = B.leases.size();
+    // per lane: the verdict of the block it verified last (device int64 at the start of its buffer)
+    std::vector<unsigned long long> verdict(n_blocks, ~0ull);
+    std::vector<size_t> lane_last(lanes, SIZE_MAX);
+    for (size_t i = 0; i < n_blocks; i++) {
+        if (first_bad_out) first_bad_out[i] = -1;
+        const size_t n_exp = meta_lens[i] / 4, n_act = div_up(lens[i], chunk);
+        if (n_exp != n_act) { status_out[i] = GPU_EC_ERR_COUNT_MISMATCH; continue; }   // chunkserver.rs:277-279
+        status_out[i] = GPU_EC_OK;
+        if (n_act == 0) continue;
+        if (!data[i] || !meta_be[i]) return GPU_EC_ERR_INVALID_ARG;
+        Lease &l = B.leases[i % lanes];
+        CK(cudaSetDevice(l.d->ordinal));
+        cudaStream_t st = l.s->stream;
+        const size_t data_off = 256, meta_off = data_off + round_up(lens[i], 256);
+        RET(slot_reserve(*l.s, meta_off + round_up(4 * n_act, 256) + 256));
+        uint8_t *db = l.s->dbuf;
+        unsigned long long *d_bad = reinterpret_cast<unsigned long long *>(db);
+        // the slot's previous verdict was copied out in stream order before this memset runs
+        CK(cudaMemsetAsync(d_bad, 0xFF, 8, st));
+        CK(cudaMemcpyAsync(db + data_off, data[i], lens[i], cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(db + meta_off, meta_be[i], 4 * n_act, cudaMemcpyHostToDevice, st));
+        CrcJob j;
+        j.base = db + data_off; j.n_buf = 1; j.buf_stride = round_up(lens[i], 256); j.len = lens[i]; j.chunk = chunk; j.poly = poly;
+        j.expect_be = db + meta_off; j.first_bad = d_bad;
+        RET(launch_crc(*l.d, j, st));
+        CK(cudaMemcpyAsync(&verdict[i], d_bad, 8, cudaMemcpyDeviceToHost, st));
+        lane_last[i % lanes] = i;
+    }
+    RET(B.sync_all());
+    for (size_t i = 0; i < n_blocks; i++) {
+        if (status_out[i] == GPU_EC_OK && verdict[i] != ~0ull) {
+            status_out[i] = GPU_EC_ERR_CRC_MISMATCH;
+            if (first_bad_out) first_bad_out[i] = static_cast<int64_t>(verdict[i]);
+        }
+    }
+    return GPU_EC_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // gpu_ec_crc32_dev_noalloc — whole-buffer CRCs for callers that are not allowed to allocate.
 //

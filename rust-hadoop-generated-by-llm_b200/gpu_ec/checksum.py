@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-from typing import Optional
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -85,12 +85,74 @@ def check_expected(data, expected_checksum: int) -> Optional[str]:
     return None
 
 
+def verify_blocks(blocks: Sequence, metas: Sequence[bytes], chunk: int = CHECKSUM_CHUNK_SIZE,
+                  poly: int = POLY_IEEE) -> List[Optional[str]]:
+    """Batched verify_block (the scrubber's inner loop, chunkserver.rs:664-690): one call, blocks
+    pipelined over streams. -> per block None or the reference's error string."""
+    n = len(blocks)
+    arrs = [_as_u8(b) for b in blocks]
+    mbs = [np.frombuffer(bytes(m), dtype=np.uint8) for m in metas]
+    dptr = (C.c_void_p * n)(*[a.ctypes.data if a.size else None for a in arrs])
+    mptr = (C.c_void_p * n)(*[m.ctypes.data if m.size else None for m in mbs])
+    lens = (C.c_size_t * n)(*[a.size for a in arrs])
+    mlens = (C.c_size_t * n)(*[m.size for m in mbs])
+    status = (C.c_int * n)()
+    bad = (C.c_int64 * n)()
+    check(lib().gpu_ec_verify_chunks_batch(n, dptr, lens, chunk, poly, mptr, mlens, status, bad))
+    out: List[Optional[str]] = []
+    for i in range(n):
+        if status[i] == ERR_COUNT_MISMATCH:
+            out.append("Checksum count mismatch")
+        elif status[i] == ERR_CRC_MISMATCH:
+            out.append(f"Checksum mismatch at chunk {bad[i]}")
+        else:
+            check(status[i])
+            out.append(None)
+    return out
+
+
 class BlockStore:
     """The slice of MyChunkServer that owns `<dir>/<block_id>` + `<dir>/<block_id>.meta`."""
 
     def __init__(self, storage_dir: str, cold_storage_dir: Optional[str] = None):
         self.storage_dir = storage_dir
         self.cold_storage_dir = cold_storage_dir
+
+    def write_block_checked(self, block_id: str, data, expected_checksum: int = 0) -> Optional[str]:
+        """WriteBlock's checksum work in ONE pass over the bytes: the reference
+        hashes req.data twice, whole-block verify (chunkserver.rs:746-766) then per-512-byte
+        (:195). -> None on success or the reference's "Checksum mismatch: ..." text (nothing written)."""
+        d = _as_u8(data)
+        whole, chunks = block_checksums(d)
+        if expected_checksum != 0 and whole != expected_checksum:
+            return f"Checksum mismatch: expected {expected_checksum}, actual {whole}"
+        with open(os.path.join(self.storage_dir, block_id), "wb") as f:
+            f.write(d.tobytes())
+        with open(os.path.join(self.storage_dir, block_id + ".meta"), "wb") as f:
+            f.write(meta_bytes(chunks))
+        return None
+
+    def scrub(self) -> Tuple[int, List[str]]:
+        """run_background_scrubber's pass (chunkserver.rs:652-701): every non-.meta file of the
+        storage dir is re-verified; -> (blocks scanned, ids of corrupted blocks). One batched call."""
+        ids = sorted(n for n in os.listdir(self.storage_dir)
+                     if not n.endswith(".meta") and os.path.isfile(os.path.join(self.storage_dir, n)))
+        blocks, metas, have = [], [], []
+        bad: List[str] = []
+        for bid in ids:
+            mp = self._meta_path(bid)
+            if not os.path.exists(mp):
+                bad.append(bid)  # "Checksum file missing" counts as a failed verify
+                continue
+            with open(os.path.join(self.storage_dir, bid), "rb") as f:
+                blocks.append(np.frombuffer(f.read(), dtype=np.uint8))
+            with open(mp, "rb") as f:
+                metas.append(f.read())
+            have.append(bid)
+        for bid, err in zip(have, verify_blocks(blocks, metas)):
+            if err:
+                bad.append(bid)
+        return len(ids), sorted(bad)
 
     def write_block(self, block_id: str, data) -> None:
         """write_block_async (chunkserver.rs:192-209): data file + big-endian .meta sidecar."""

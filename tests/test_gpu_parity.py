@@ -460,3 +460,61 @@ def test_concurrent_callers(L, orc):
     [t.start() for t in th]
     [t.join() for t in th]
     assert not errs, errs
+
+
+# ------------------------------------------------------------------ callers either side of the path
+def test_scrubber_batched_verify(L, orc, tmp_path):
+    """run_background_scrubber (chunkserver.rs:642-718) as one batched verify over the storage dir."""
+    store = checksum.BlockStore(str(tmp_path))
+    sizes = {"a": 61, "b": 512, "c": 65_536, "d": 1_000_003, "e": 0, "f": 5 << 20, "g": 600}
+    for bid, n in sizes.items():
+        store.write_block(bid, rnd(n, n + 1))
+    assert store.scrub() == (7, [])
+    raw = bytearray((tmp_path / "d").read_bytes())
+    raw[777_777] ^= 0x10
+    (tmp_path / "d").write_bytes(bytes(raw))
+    (tmp_path / "g").write_bytes((tmp_path / "g").read_bytes()[:-1])     # count still matches, CRC does not
+    (tmp_path / "c").write_bytes((tmp_path / "c").read_bytes() + b"x")   # one more chunk than the .meta has
+    (tmp_path / "b.meta").unlink()                                       # "Checksum file missing"
+    assert store.scrub() == (7, ["b", "c", "d", "g"])
+    blocks = [np.frombuffer((tmp_path / b).read_bytes(), dtype=np.uint8) for b in ("a", "c", "d", "f", "g")]
+    metas = [(tmp_path / (b + ".meta")).read_bytes() for b in ("a", "c", "d", "f", "g")]
+    got = checksum.verify_blocks(blocks, metas)
+    assert got == [None, "Checksum count mismatch", f"Checksum mismatch at chunk {777_777 // 512}", None,
+                   "Checksum mismatch at chunk 1"]
+    # same verdicts as the block-by-block path
+    assert got == [checksum.verify_chunks(b, m) for b, m in zip(blocks, metas)]
+
+
+def test_write_block_checked_single_pass(L, tmp_path):
+    store = checksum.BlockStore(str(tmp_path))
+    data = rnd(300_000, 42)
+    crc = zlib.crc32(data.tobytes())
+    assert store.write_block_checked("ok", data, crc) is None
+    assert store.write_block_checked("skip", data, 0) is None  # 0 = not provided (chunkserver.rs:746)
+    store.verify_block("ok", data)
+    assert (tmp_path / "ok.meta").read_bytes() == (tmp_path / "skip.meta").read_bytes()
+    assert store.write_block_checked("bad", data, crc ^ 1) == f"Checksum mismatch: expected {crc ^ 1}, actual {crc}"
+    assert not (tmp_path / "bad").exists()
+
+
+def test_client_ec_write_read_orchestration(L, orc):
+    from gpu_ec import client
+    buf = rnd(1_000_001, 7)
+    plan = client.prepare_ec_write(buf, 6, 3)
+    want = orc.encode(buf, 6, 3)
+    assert len(plan.shards) == 9 and plan.actual_size == buf.size
+    assert all(np.array_equal(a, b) for a, b in zip(plan.shards, want))
+    assert plan.shard_checksums == [zlib.crc32(s.tobytes()) for s in want]
+    assert plan.full_checksum == zlib.crc32(buf.tobytes())
+    # fast path: all data shards present (client/src/mod.rs:1152-1161, test :1637-1650)
+    out = client.read_ec_block("blk", plan.shards[:6] + [None, None, None], 6, 3, buf.size)
+    assert np.array_equal(out, buf)
+    # degraded read (test :1652-1664)
+    opt = [s.copy() for s in plan.shards]
+    opt[0] = None
+    opt[5] = None
+    opt[8] = None
+    assert np.array_equal(client.read_ec_block("blk", opt, 6, 3, buf.size), buf)
+    with pytest.raises(erasure.ErasureError, match="EC block blk unrecoverable: only 5/6 shards available"):
+        client.read_ec_block("blk", [None] * 4 + list(plan.shards[4:]), 6, 3, buf.size)
