@@ -251,23 +251,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
     const unsigned long long n_clusters = gridDim.x >> 1;
     unsigned long long t = blockIdx.x >> 1;
 
+    // loop-invariant addressing: per-input and per-owned-row byte offsets, and the (stripe, tile in
+    // stripe) pair advanced incrementally so the loop has no division and no 64-bit index math
+    const uint8_t *in_ptr[KH];
+#pragma unroll
+    for (int j = 0; j < KH; j++)
+        in_ptr[j] = p.base + static_cast<unsigned long long>(p.in_idx[(j < ni) ? (j_base + j) : j_base]) * p.shard_stride;
+    uint8_t *out_ptr0 = p.base + static_cast<unsigned long long>(p.out_idx[n_own > 0 ? own0 : 0]) * p.shard_stride;
+    uint8_t *out_ptr1 = p.base + static_cast<unsigned long long>(p.out_idx[n_own > 1 ? own0 + 1 : 0]) * p.shard_stride;
+    const unsigned int tps = p.tiles_per_stripe;
+    const unsigned long long step_stripe = n_clusters / tps;
+    const unsigned int step_tt = static_cast<unsigned int>(n_clusters - step_stripe * tps);
+    unsigned long long nstripe = t / tps;                       // position of the NEXT tile to locate
+    unsigned int ntt = static_cast<unsigned int>(t - nstripe * tps);
+
     uint4 cur[KH];
-    auto locate = [&](unsigned long long tile, unsigned long long &off) -> bool {
-        const unsigned long long stripe = tile / p.tiles_per_stripe;
-        const unsigned int tt = static_cast<unsigned int>(tile - stripe * p.tiles_per_stripe);
-        const unsigned int v = tt * RS_THREADS + threadIdx.x;
-        off = stripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+    auto locate_next = [&](unsigned long long &off) -> bool {   // locate (nstripe, ntt), then advance by one step
+        const unsigned int v = ntt * RS_THREADS + threadIdx.x;
+        off = nstripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+        nstripe += step_stripe;
+        ntt += step_tt;
+        if (ntt >= tps) { ntt -= tps; nstripe++; }
         return v < p.nvec;
     };
     auto load = [&](uint4 (&d)[KH], unsigned long long off, bool ok) {
 #pragma unroll
         for (int j = 0; j < KH; j++)
-            d[j] = (ok && j < ni) ? ld_vec(p.base + off + static_cast<unsigned long long>(p.in_idx[j_base + j]) * p.shard_stride)
-                                  : make_uint4(0, 0, 0, 0);
+            d[j] = (ok && j < ni) ? ld_vec(in_ptr[j] + off) : make_uint4(0, 0, 0, 0);
     };
     unsigned long long cur_off = 0;
     bool cur_ok = false;
-    if (t < p.n_tiles) { cur_ok = locate(t, cur_off); load(cur, cur_off, cur_ok); }
+    if (t < p.n_tiles) { cur_ok = locate_next(cur_off); load(cur, cur_off, cur_ok); }
 
     uint4 keep0 = make_uint4(0, 0, 0, 0), keep1 = keep0;  // the rows this CTA owns, from the previous tile
     unsigned long long keep_off = 0;
@@ -287,9 +301,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
             __syncwarp();                                                                                            \
             if (lane == 0) mbar_arrive_peer(peer_empty + ps_ * (NW * 8)); /* slot may be overwritten */              \
             if (keep_ok) {                                                                                           \
-                *reinterpret_cast<uint4 *>(p.base + keep_off + static_cast<unsigned long long>(p.out_idx[own0]) * p.shard_stride) = o0_; \
-                if (n_own > 1)                                                                                       \
-                    *reinterpret_cast<uint4 *>(p.base + keep_off + static_cast<unsigned long long>(p.out_idx[own0 + 1]) * p.shard_stride) = o1_; \
+                *reinterpret_cast<uint4 *>(out_ptr0 + keep_off) = o0_;                                               \
+                if (n_own > 1) *reinterpret_cast<uint4 *>(out_ptr1 + keep_off) = o1_;                                \
             }                                                                                                        \
         }                                                                                                            \
     } while (0)
@@ -298,7 +311,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
         uint4 nxt[KH];
         unsigned long long nxt_off = 0;
         bool nxt_ok = false;
-        if (t + n_clusters < p.n_tiles) nxt_ok = locate(t + n_clusters, nxt_off);
+        if (t + n_clusters < p.n_tiles) nxt_ok = locate_next(nxt_off);
         load(nxt, nxt_off, nxt_ok);
 
         uint32_t acc[16];
