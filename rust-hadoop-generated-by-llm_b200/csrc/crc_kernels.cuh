@@ -125,6 +125,12 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
 
     unsigned long long tile = static_cast<unsigned long long>(blockIdx.x) * CRC_WARPS + warp;
     unsigned int col = 0;
+    // (buffer, first segment) of `tile`, advanced incrementally: no division in the loop
+    const unsigned long long tpb = p.tiles_per_buf;
+    const unsigned long long step_buf = wstep / tpb;
+    const unsigned long long step_til = wstep - step_buf * tpb;
+    unsigned long long t_buf = tpb ? tile / tpb : 0;
+    unsigned long long t_til = tile - t_buf * tpb;
     // number of column slices row `seg` of a buffer has
     auto cols_of = [&](unsigned long long seg) -> unsigned int {
         return seg < p.nfull ? ncol : (seg == p.nfull ? ncol_rag : 0u);
@@ -136,9 +142,8 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
     const uint32_t mbar = static_cast<uint32_t>(__cvta_generic_to_shared(crc_smem + CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES)) + warp * 8;
     uint32_t phase = 0;
-    auto issue_loads = [&](unsigned long long tl_, unsigned int c_) {
-        const unsigned long long buf = tl_ / p.tiles_per_buf;
-        const unsigned long long seg = (tl_ - buf * p.tiles_per_buf) * 32ull + lane;
+    auto issue_loads = [&](unsigned long long buf, unsigned long long til, unsigned int c_) {
+        const unsigned long long seg = til * 32ull + lane;
         const bool valid = c_ < cols_of(seg);
         const unsigned int n = __popc(__ballot_sync(0xffffffffu, valid));
         if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(n * 128u) : "memory");
@@ -162,9 +167,8 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     // global -> shared without touching registers or allocating in L1 (cp.async.cg, 16 bytes per
     // lane): the box is filled for slice (tl_, c_) while the previous slice is hashed from registers
     const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
-    auto issue_loads = [&](unsigned long long tl_, unsigned int c_) {
-        const unsigned long long buf = tl_ / p.tiles_per_buf;
-        const unsigned long long seg0 = (tl_ - buf * p.tiles_per_buf) * 32ull;
+    auto issue_loads = [&](unsigned long long buf, unsigned long long til, unsigned int c_) {
+        const unsigned long long seg0 = til * 32ull;
         const uint8_t *src = p.base + buf * p.buf_stride + seg0 * p.G + static_cast<unsigned long long>(c_) * 128ull + scol * 16;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
@@ -181,7 +185,7 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
 #endif
     // a tile whose only row is a short ragged segment may have zero full slices: still one pass
     const unsigned int ncol_loop = ncol ? ncol : 1u;
-    if (tile < n_tiles) issue_loads(tile, 0);
+    if (tile < n_tiles) issue_loads(t_buf, t_til, 0);
     uint32_t c = 0xFFFFFFFFu;
     while (tile < n_tiles) {
         wait_loads();
@@ -192,13 +196,18 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
         for (int q = 0; q < 8; q++) v[q] = box_read(q);
         __syncwarp();
         // advance; the next slice streams into the box while this one is hashed
-        const unsigned long long cur_tile = tile;
+        const unsigned long long buf = t_buf;
+        const unsigned long long seg = t_til * 32ull + lane;
         const unsigned int cur_col = col;
         const bool last_col = (col + 1 == ncol_loop);
-        if (last_col) { tile += wstep; col = 0; } else { col++; }
-        if (tile < n_tiles) issue_loads(tile, col);
-        const unsigned long long buf = cur_tile / p.tiles_per_buf;
-        const unsigned long long seg = (cur_tile - buf * p.tiles_per_buf) * 32ull + lane;
+        if (last_col) {
+            tile += wstep; col = 0;
+            t_buf += step_buf; t_til += step_til;
+            if (t_til >= tpb) { t_til -= tpb; t_buf++; }
+        } else {
+            col++;
+        }
+        if (tile < n_tiles) issue_loads(t_buf, t_til, col);
         if (cur_col < cols_of(seg)) {
 #pragma unroll
             for (int q = 0; q < 8; q++) {

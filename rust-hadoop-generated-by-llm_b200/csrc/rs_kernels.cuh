@@ -106,30 +106,43 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
     unsigned long long t = blockIdx.x;
     if (t >= p.n_tiles) return;
 
+    // loop-invariant addressing: per-shard byte offsets, and the (stripe, tile in stripe) pair
+    // advanced incrementally so the loop has no division
+    const uint8_t *in_ptr[K];
+#pragma unroll
+    for (int j = 0; j < K; j++) in_ptr[j] = p.base + static_cast<unsigned long long>(p.in_idx[j]) * p.shard_stride;
+    uint8_t *out_ptr[RS_MAX_OUT];
+#pragma unroll
+    for (int r = 0; r < RS_MAX_OUT; r++) out_ptr[r] = p.base + static_cast<unsigned long long>(p.out_idx[r < p.n_out ? r : 0]) * p.shard_stride;
+    const unsigned int tps = p.tiles_per_stripe;
+    const unsigned long long step_stripe = step / tps;
+    const unsigned int step_tt = static_cast<unsigned int>(step - step_stripe * tps);
+    unsigned long long nstripe = t / tps;
+    unsigned int ntt = static_cast<unsigned int>(t - nstripe * tps);
+
     uint4 cur[K];
     bool cur_ok;
     unsigned long long cur_off;
-    auto locate = [&](unsigned long long tile, unsigned long long &off) -> bool {
-        const unsigned long long stripe = tile / p.tiles_per_stripe;
-        const unsigned int tt = static_cast<unsigned int>(tile - stripe * p.tiles_per_stripe);
-        const unsigned int v = tt * RS_THREADS + threadIdx.x;
-        off = stripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+    auto locate_next = [&](unsigned long long &off) -> bool {
+        const unsigned int v = ntt * RS_THREADS + threadIdx.x;
+        off = nstripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
+        nstripe += step_stripe;
+        ntt += step_tt;
+        if (ntt >= tps) { ntt -= tps; nstripe++; }
         return v < p.nvec;
     };
     auto load = [&](uint4 (&d)[K], unsigned long long off, bool ok) {
 #pragma unroll
-        for (int j = 0; j < K; j++)
-            d[j] = ok ? ld_vec(p.base + off + static_cast<unsigned long long>(p.in_idx[j]) * p.shard_stride)
-                      : make_uint4(0, 0, 0, 0);
+        for (int j = 0; j < K; j++) d[j] = ok ? ld_vec(in_ptr[j] + off) : make_uint4(0, 0, 0, 0);
     };
-    cur_ok = locate(t, cur_off);
+    cur_ok = locate_next(cur_off);
     load(cur, cur_off, cur_ok);
 
     for (; t < p.n_tiles; t += step) {
         uint4 nxt[K];
         unsigned long long nxt_off = 0;
         bool nxt_ok = false;
-        if (t + step < p.n_tiles) nxt_ok = locate(t + step, nxt_off);
+        if (t + step < p.n_tiles) nxt_ok = locate_next(nxt_off);
         load(nxt, nxt_off, nxt_ok);
 
         if (cur_ok) {
@@ -154,7 +167,7 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
 #pragma unroll
             for (int r = 0; r < RS_MAX_OUT; r++) {
                 if (r < p.n_out) {
-                    uint4 *dst = reinterpret_cast<uint4 *>(p.base + cur_off + static_cast<unsigned long long>(p.out_idx[r]) * p.shard_stride);
+                    uint4 *dst = reinterpret_cast<uint4 *>(out_ptr[r] + cur_off);
                     uint4 v = make_uint4(o[0][r], o[1][r], o[2][r], o[3][r]);
                     if (p.accumulate) { const uint4 old = *dst; v.x ^= old.x; v.y ^= old.y; v.z ^= old.z; v.w ^= old.w; }
                     *dst = v;
