@@ -142,8 +142,11 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
     const uint32_t mbar = static_cast<uint32_t>(__cvta_generic_to_shared(crc_smem + CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES)) + warp * 8;
     uint32_t phase = 0;
-    auto issue_loads = [&](unsigned long long buf, unsigned long long til, unsigned int c_) {
-        const unsigned long long seg = til * 32ull + lane;
+    unsigned long long tma_buf = 0, tma_til = 0;
+    auto enter_tile = [&](unsigned long long buf, unsigned long long til) { tma_buf = buf; tma_til = til; };
+    auto issue_loads = [&](unsigned int c_) {
+        const unsigned long long buf = tma_buf;
+        const unsigned long long seg = tma_til * 32ull + lane;
         const bool valid = c_ < cols_of(seg);
         const unsigned int n = __popc(__ballot_sync(0xffffffffu, valid));
         if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(n * 128u) : "memory");
@@ -165,18 +168,41 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     auto box_read = [&](int q) -> uint4 { return *reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(box) + lane * CRC_ROW_BYTES + q * 16); };
 #else
     // global -> shared without touching registers or allocating in L1 (cp.async.cg, 16 bytes per
-    // lane): the box is filled for slice (tl_, c_) while the previous slice is hashed from registers
+    // lane): the box is filled for slice (tile, c_) while the previous slice is hashed from registers.
+    // Per tile the lane's 8 staging rows are classified once (bit i of full_mask: row i*4+srow is a
+    // full segment; rag_i: which of them, if any, is the buffer's ragged segment), so a slice costs
+    // 8 predicated copies and a handful of 32-bit adds.
     const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
-    auto issue_loads = [&](unsigned long long buf, unsigned long long til, unsigned int c_) {
+    uint32_t dst_of[8];
+    unsigned int row_off[8];  // row * G (G <= 64 KiB, 32 rows: fits 32 bits)
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const unsigned int row = i * 4 + srow;
+        dst_of[i] = box_s + (row * 8 + (scol ^ (row & 7))) * 16;
+        row_off[i] = row * p.G;
+    }
+    const uint8_t *tile_src = nullptr;
+    unsigned int full_mask = 0;
+    int rag_i = -1;
+    auto enter_tile = [&](unsigned long long buf, unsigned long long til) {
         const unsigned long long seg0 = til * 32ull;
-        const uint8_t *src = p.base + buf * p.buf_stride + seg0 * p.G + static_cast<unsigned long long>(c_) * 128ull + scol * 16;
+        tile_src = p.base + buf * p.buf_stride + seg0 * p.G + scol * 16;
+        const unsigned long long left = p.nfull > seg0 ? p.nfull - seg0 : 0;  // full rows from seg0 on
+        full_mask = 0;
+        rag_i = -1;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             const unsigned int row = i * 4 + srow;
-            if (c_ < cols_of(seg0 + row)) {
-                const uint32_t dst = box_s + (row * 8 + (scol ^ (row & 7))) * 16;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + static_cast<unsigned long long>(row) * p.G) : "memory");
-            }
+            if (row < left) full_mask |= 1u << i;
+            else if (p.rag && row == left) rag_i = i;
+        }
+    };
+    auto issue_loads = [&](unsigned int c_) {
+        const uint8_t *src = tile_src + (static_cast<unsigned long long>(c_) << 7);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (((full_mask >> i) & 1u) || (i == rag_i && c_ < ncol_rag))
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_of[i]), "l"(src + row_off[i]) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -185,7 +211,7 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
 #endif
     // a tile whose only row is a short ragged segment may have zero full slices: still one pass
     const unsigned int ncol_loop = ncol ? ncol : 1u;
-    if (tile < n_tiles) issue_loads(t_buf, t_til, 0);
+    if (tile < n_tiles) { enter_tile(t_buf, t_til); issue_loads(0); }
     uint32_t c = 0xFFFFFFFFu;
     while (tile < n_tiles) {
         wait_loads();
@@ -204,10 +230,11 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
             tile += wstep; col = 0;
             t_buf += step_buf; t_til += step_til;
             if (t_til >= tpb) { t_til -= tpb; t_buf++; }
+            if (tile < n_tiles) enter_tile(t_buf, t_til);
         } else {
             col++;
         }
-        if (tile < n_tiles) issue_loads(t_buf, t_til, col);
+        if (tile < n_tiles) issue_loads(col);
         if (cur_col < cols_of(seg)) {
 #pragma unroll
             for (int q = 0; q < 8; q++) {

@@ -77,3 +77,35 @@ if __name__ == "__main__":
         rs(10, 4, 64 << 20, 48)
     elif what == "rs63":
         rs(6, 3, 64 << 20, 64)
+
+
+def scale():
+    """Does RS(10,4) / RS(6,3) throughput depend on the resident size (TLB / DRAM) or on clocks?"""
+    import subprocess, threading, time
+    for k, m, n in ((10, 4, 48), (10, 4, 1024), (6, 3, 64), (6, 3, 1000)):
+        S = gpu_ec.erasure.shard_len(64 << 20, k)
+        b = device.StripeBatch(n, k, m, S)
+        b.fill_synthetic(4)
+        torch.cuda.synchronize()
+        proc = subprocess.Popen(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader,nounits", "-lms", "20"],
+                                stdout=subprocess.PIPE, text=True)
+        lines = []
+        th = threading.Thread(target=lambda: lines.extend(proc.stdout), daemon=True)
+        th.start()
+        time.sleep(0.1)
+        steps = max(5, 400 // max(1, n // 48))
+        ms = timed(b.encode, steps, 3)
+        time.sleep(0.05)
+        proc.terminate()
+        th.join(timeout=2)
+        clk = sorted(float(x.split(",")[0]) for x in lines if "," in x)
+        pw = sorted(float(x.split(",")[1]) for x in lines if "," in x)
+        a = (k + m) * S * n
+        print(f"rs({k},{m}) n={n}: {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f} steps={steps} "
+              f"clk min/med/max={clk[0]:.0f}/{clk[len(clk)//2]:.0f}/{clk[-1]:.0f} power med/max={pw[len(pw)//2]:.0f}/{pw[-1]:.0f} W")
+        del b
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__" and sys.argv[1] == "scale":
+    scale()
