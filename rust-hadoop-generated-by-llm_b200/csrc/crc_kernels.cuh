@@ -34,20 +34,19 @@ namespace gpu_ec {
 #endif
 constexpr int CRC_WARPS = GPU_EC_CRC_WARPS;
 constexpr int CRC_THREADS = CRC_WARPS * 32;
-constexpr int CRC_TAB_BYTES = 4 * 256 * 32 * 4;            // 128 KiB
-// Staging variant. 0 (default): cp.async.cg 16-byte copies. 1: one 128-byte TMA bulk copy per row
-// (cp.async.bulk + mbarrier). Measured on B200 over 1 GiB: 4490 GB/s vs 3325 GB/s per 512-byte chunks:
-// 128-byte bulk copies are too small to amortise the TMA's per-request cost, so 0 ships.
-#ifndef GPU_EC_CRC_TMA
-#define GPU_EC_CRC_TMA 0
-#endif
-#if GPU_EC_CRC_TMA
-constexpr int CRC_ROW_BYTES = 144;                         // 128 data + 16 pad: row-per-lane LDS.128 is conflict-free
-#else
-constexpr int CRC_ROW_BYTES = 128;                         // XOR-swizzled 16-byte chunks instead of padding
-#endif
+constexpr int CRC_ROW_BYTES = 128;                         // XOR-swizzled 16-byte chunks, no padding
 constexpr int CRC_BOX_BYTES = 32 * CRC_ROW_BYTES;          // per-warp staging box
-constexpr int CRC_SMEM_BYTES = CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES + CRC_WARPS * 8;  // tables + boxes + mbarriers
+// Shared-memory map (shared-window addresses; the dynamic window starts at s0, 1 KiB on sm_100):
+//   [s0, 0x10000)        staging boxes of the first warps
+//   [0x10000, 0x20000)   table block A: T3 and T2 interleaved, entry b at A + b*256 + {0,128} + lane*4
+//   [0x20000, 0x30000)   table block B: T1 and T0 interleaved the same way
+//   [0x30000, ...)       staging boxes of the remaining warps
+// Blocks are 64 KiB aligned and rows 256 B, so an address is {block base | data byte | lane*4}
+// byte for byte: ONE PRMT assembles it (no shift, no multiply-add) and the table half is the LDS
+// immediate: 2 instructions per lookup instead of 3.
+constexpr uint32_t CRC_BLK_A = 0x10000u, CRC_BLK_B = 0x20000u, CRC_REGION2 = 0x30000u;
+constexpr int CRC_TAB_BYTES = 4 * 256 * 32 * 4;            // 128 KiB
+constexpr int CRC_SMEM_BYTES = 232448;                     // the whole 227 KiB opt-in window
 
 // slice-by-4 tables for both polynomials, filled once per device by the host (host_math.hpp)
 __device__ uint32_t g_crc_tab[2][4][256];
@@ -83,34 +82,44 @@ __device__ __forceinline__ void crc_emit(const CrcParams &p, unsigned long long 
 
 __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __grid_constant__ CrcParams p) {
     extern __shared__ __align__(128) unsigned char crc_smem[];
-    uint32_t *tab = reinterpret_cast<uint32_t *>(crc_smem);
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
+    const uint32_t s0 = static_cast<uint32_t>(__cvta_generic_to_shared(crc_smem));
+    if (s0 > 0x1000u) __trap();  // the map above assumes the dynamic window starts in the first 4 KiB
     // replicate the 4 KiB table 32 times: one coalesced global load per lane, then each entry is
-    // broadcast into its 32 lane copies (tab[entry*32 + lane])
+    // broadcast into its 32 lane copies. Table t (T3,T2 -> block A; T1,T0 -> block B), half = !(t&1).
     for (int e0 = warp * 32; e0 < 1024; e0 += CRC_WARPS * 32) {
         const int e = e0 + lane;
         const uint32_t v = g_crc_tab[p.poly][e >> 8][e & 255];
 #pragma unroll 8
-        for (int q = 0; q < 32; q++) tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+        for (int q = 0; q < 32; q++) {
+            const int eq = e0 + q, t = eq >> 8, bq = eq & 255;
+            const uint32_t addr = ((t >= 2) ? CRC_BLK_A : CRC_BLK_B) + bq * 256 + ((t & 1) ? 0 : 128) + lane * 4;
+            const uint32_t vq = __shfl_sync(0xffffffffu, v, q);
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(vq) : "memory");
+        }
     }
-#if GPU_EC_CRC_TMA
-    if (lane == 0) {
-        const uint32_t mb = static_cast<uint32_t>(__cvta_generic_to_shared(crc_smem + CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES)) + warp * 8;
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-#endif
     __syncthreads();
 
-    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(tab)) + lane * 4;
-    uint4 *box = reinterpret_cast<uint4 *>(crc_smem + CRC_TAB_BYTES + warp * CRC_BOX_BYTES);
+    // staging box of this warp: below block A while there is room, the rest above block B
+    const uint32_t s0a = (s0 + 127u) & ~127u;
+    const int n1 = static_cast<int>((CRC_BLK_A - s0a) / CRC_BOX_BYTES);
+    const uint32_t box_s = (warp < n1) ? (s0a + warp * CRC_BOX_BYTES) : (CRC_REGION2 + (warp - n1) * CRC_BOX_BYTES);
+    const uint4 *box = reinterpret_cast<const uint4 *>(crc_smem + (box_s - s0));
+    const uint32_t lb_a = CRC_BLK_A | static_cast<uint32_t>(lane * 4), lb_b = CRC_BLK_B | static_cast<uint32_t>(lane * 4);
+    // table[byte I of c]: address = {block | byte | lane*4} by one PRMT, table half in the immediate
+#define CRC_LUT(LB, HALF, C, I)                                                                         \
+    ([&]() -> uint32_t {                                                                                \
+        uint32_t v_;                                                                                    \
+        asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v_) : "r"(__byte_perm((C), (LB), 0x7604 | ((I) << 4))), "n"((HALF) * 128)); \
+        return v_;                                                                                      \
+    }())
     auto step_word = [&](uint32_t c, uint32_t w) -> uint32_t {
         c ^= w;
-        const uint32_t a = lut_lds<3 * 32768>(tl, byte_of<0>(c));
-        const uint32_t b = lut_lds<2 * 32768>(tl, byte_of<1>(c));
-        const uint32_t d = lut_lds<1 * 32768>(tl, byte_of<2>(c));
-        const uint32_t e = lut_lds<0>(tl, c >> 24);
+        const uint32_t a = CRC_LUT(lb_a, 0, c, 0);  // T3[byte 0]
+        const uint32_t b = CRC_LUT(lb_a, 1, c, 1);  // T2[byte 1]
+        const uint32_t d = CRC_LUT(lb_b, 0, c, 2);  // T1[byte 2]
+        const uint32_t e = CRC_LUT(lb_b, 1, c, 3);  // T0[byte 3]
         return a ^ b ^ d ^ e;
     };
 
@@ -118,10 +127,8 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     const unsigned int ncol_rag = p.rag >> 7;  // whole slices of the ragged segment
     const unsigned long long n_tiles = p.n_buf * p.tiles_per_buf;
     const unsigned long long wstep = static_cast<unsigned long long>(gridDim.x) * CRC_WARPS;
-#if !GPU_EC_CRC_TMA
     // staging roles: 8 lanes cover one 128-byte row slice, 4 rows per copy instruction
     const int srow = lane >> 3, scol = lane & 7;
-#endif
 
     unsigned long long tile = static_cast<unsigned long long>(blockIdx.x) * CRC_WARPS + warp;
     unsigned int col = 0;
@@ -135,44 +142,11 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     auto cols_of = [&](unsigned long long seg) -> unsigned int {
         return seg < p.nfull ? ncol : (seg == p.nfull ? ncol_rag : 0u);
     };
-#if GPU_EC_CRC_TMA
-    // global -> shared through the TMA (async proxy): lane r issues ONE 128-byte bulk copy for row r
-    // of the slice; completion is counted in bytes on the warp's mbarrier. No register staging, no
-    // L1 allocation, and the box is written without spending LSU issue slots or LSU wavefronts.
-    const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
-    const uint32_t mbar = static_cast<uint32_t>(__cvta_generic_to_shared(crc_smem + CRC_TAB_BYTES + CRC_WARPS * CRC_BOX_BYTES)) + warp * 8;
-    uint32_t phase = 0;
-    unsigned long long tma_buf = 0, tma_til = 0;
-    auto enter_tile = [&](unsigned long long buf, unsigned long long til) { tma_buf = buf; tma_til = til; };
-    auto issue_loads = [&](unsigned int c_) {
-        const unsigned long long buf = tma_buf;
-        const unsigned long long seg = tma_til * 32ull + lane;
-        const bool valid = c_ < cols_of(seg);
-        const unsigned int n = __popc(__ballot_sync(0xffffffffu, valid));
-        if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(n * 128u) : "memory");
-        __syncwarp();
-        if (valid) {
-            const uint8_t *src = p.base + buf * p.buf_stride + seg * p.G + static_cast<unsigned long long>(c_) * 128ull;
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 128, [%2];" ::"r"(box_s + lane * CRC_ROW_BYTES),
-                         "l"(src), "r"(mbar)
-                         : "memory");
-        }
-    };
-    auto wait_loads = [&]() {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(mbar),
-            "r"(phase)
-            : "memory");
-        phase ^= 1u;
-    };
-    auto box_read = [&](int q) -> uint4 { return *reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(box) + lane * CRC_ROW_BYTES + q * 16); };
-#else
     // global -> shared without touching registers or allocating in L1 (cp.async.cg, 16 bytes per
     // lane): the box is filled for slice (tile, c_) while the previous slice is hashed from registers.
     // Per tile the lane's 8 staging rows are classified once (bit i of full_mask: row i*4+srow is a
     // full segment; rag_i: which of them, if any, is the buffer's ragged segment), so a slice costs
     // 8 predicated copies and a handful of 32-bit adds.
-    const uint32_t box_s = static_cast<uint32_t>(__cvta_generic_to_shared(box));
     uint32_t dst_of[8];
     unsigned int row_off[8];  // row * G (G <= 64 KiB, 32 rows: fits 32 bits)
 #pragma unroll
@@ -208,7 +182,6 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     };
     auto wait_loads = [&]() { asm volatile("cp.async.wait_group 0;" ::: "memory"); };
     auto box_read = [&](int q) -> uint4 { return box[lane * 8 + (q ^ (lane & 7))]; };
-#endif
     // a tile whose only row is a short ragged segment may have zero full slices: still one pass
     const unsigned int ncol_loop = ncol ? ncol : 1u;
     if (tile < n_tiles) { enter_tile(t_buf, t_til); issue_loads(0); }
@@ -253,12 +226,13 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
                 const unsigned int left = p.rag & 127u;
                 unsigned int i = 0;
                 for (; i + 4 <= left; i += 4) c = step_word(c, *reinterpret_cast<const uint32_t *>(src + i));
-                for (; i < left; i++) c = (c >> 8) ^ lut_lds<0>(tl, (c ^ src[i]) & 0xffu);
+                for (; i < left; i++) c = (c >> 8) ^ CRC_LUT(lb_b, 1, c ^ src[i], 0);
                 crc_emit(p, buf, seg, ~c);
             }
             c = 0xFFFFFFFFu;
         }
     }
+#undef CRC_LUT
 }
 
 // Generic fallback for chunk sizes that are not a multiple of 128 or unaligned buffers: one
