@@ -70,11 +70,13 @@ struct Ctx {
 };
 static Ctx &ctx() { static Ctx c; return c; }
 
-static constexpr int x2_smem_bytes(int kh) { return kh * 256 * 32 * 4 + RS_X2_XBUF_BYTES + RS_X2_MBAR_BYTES; }
+// kernels in the single-PRMT layout (lut_common.cuh) address the shared window absolutely, up to 0x30000
+static constexpr int x2_smem_bytes(int kh) { return kh <= 4 ? LUT_FAST_RS_BYTES : kh * 256 * 32 * 4 + RS_X2_XBUF_BYTES + RS_X2_MBAR_BYTES; }
+static constexpr int lut8_smem_bytes(int k) { return k <= 5 ? LUT_FAST_RS_BYTES : k * 256 * 32 * 4; }
 
 template <int K>
 static int set_lut8_attr() {
-    CK(cudaFuncSetAttribute(rs_lut8_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 256 * 32 * 4));
+    CK(cudaFuncSetAttribute(rs_lut8_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(K)));
     return GPU_EC_OK;
 }
 
@@ -220,7 +222,7 @@ static int check_stripes(const gpu_ec_stripes *s) {
 
 template <int K>
 static void launch_lut8(const RsParams &p, int grid, cudaStream_t st) {
-    rs_lut8_kernel<K><<<grid, RS_THREADS, K * 256 * 32 * 4, st>>>(p);
+    rs_lut8_kernel<K><<<grid, RS_THREADS, lut8_smem_bytes(K), st>>>(p);
 }
 
 // one kernel launch: out slot out_idx[r] (r < no) (^)= XOR_{j<ni} rows[r][j] * in slot in_idx[j]

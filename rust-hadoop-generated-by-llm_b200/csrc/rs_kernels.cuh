@@ -80,7 +80,36 @@ __device__ __forceinline__ void transpose4x4(const uint32_t a[4], uint32_t o[4])
     o[3] = __byte_perm(t1, t3, 0x7632);
 }
 
+// 16-byte read-only load. The RS kernels keep their shared-memory request at <= 192.5 KiB: their
+// LDG path needs the remaining L1 (with the whole 227 KiB window requested RS(6,3) fell from 0.98 to
+// 0.77 of HBM peak, with or without L1::no_allocate; measured).
 __device__ __forceinline__ uint4 ld_vec(const uint8_t *p) { return __ldg(reinterpret_cast<const uint4 *>(p)); }
+
+// acc[q*4+b] ^= table_j[byte b of word q of d[j]] for all j < K: the lookup phase shared by the
+// byte-LUT kernels. FAST selects the single-PRMT layout of lut_common.cuh, else tables sit at
+// tl + j*32 KiB with 128-byte rows.
+template <int K, bool FAST, int J = 0>
+__device__ __forceinline__ void rs_accumulate(const uint4 (&d)[K], uint32_t (&acc)[16], uint32_t tl, uint32_t lane4) {
+    if constexpr (J < K) {
+        const uint32_t w[4] = {d[J].x, d[J].y, d[J].z, d[J].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if constexpr (FAST) {
+                acc[q * 4 + 0] ^= lut_fast<J, 0>(lane4, w[q]);
+                acc[q * 4 + 1] ^= lut_fast<J, 1>(lane4, w[q]);
+                acc[q * 4 + 2] ^= lut_fast<J, 2>(lane4, w[q]);
+                acc[q * 4 + 3] ^= lut_fast<J, 3>(lane4, w[q]);
+            } else {
+                const uint32_t tj = tl + J * (256 * 32 * 4);
+                acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
+                acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
+                acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
+                acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
+            }
+        }
+        rs_accumulate<K, FAST, J + 1>(d, acc, tl, lane4);
+    }
+}
 
 // ---------------------------------------------------------------------------------------------
 // rs_lut8: full-byte packed LUT, lane-replicated, n_in = K <= 7.
@@ -92,16 +121,27 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
     const int warp = threadIdx.x >> 5;
     constexpr int NW = RS_THREADS / 32;
 
+    // K <= 5: fast layout (single-PRMT addressing for tables 0..3, table 4 in [0x8000,0x10000); the
+    // window ends at 0x30000 = 191 KiB). K = 6, 7 keep the classic layout [K][256][32] from the window
+    // start: a sixth table would push the request past 192 KiB and starve the L1 the loads need.
+    constexpr bool FAST = (K <= 5);
+    const uint32_t s0 = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab));
+    if (FAST && s0 > LUT_FRAG1) __trap();  // not a cluster kernel: the window starts at 0
     // build the table: each lane computes one entry, the warp broadcasts it into the 32 lane copies
     for (int e0 = warp * 32; e0 < K * 256; e0 += NW * 32) {
         const int e = e0 + lane;
         const uint32_t v = packed_products(p, e >> 8, static_cast<uint32_t>(e & 255));
 #pragma unroll 8
-        for (int q = 0; q < 32; q++) rs_tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+        for (int q = 0; q < 32; q++) {
+            const int eq = e0 + q;
+            const uint32_t addr = FAST ? lut_fast_addr(eq >> 8, static_cast<uint32_t>(eq & 255), lane) : s0 + (eq * 32 + lane) * 4;
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(__shfl_sync(0xffffffffu, v, q)) : "memory");
+        }
     }
     __syncthreads();
 
-    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab)) + lane * 4;
+    const uint32_t tl = s0 + lane * 4;
+    const uint32_t lane4 = lane * 4;
     const unsigned long long step = gridDim.x;
     unsigned long long t = blockIdx.x;
     if (t >= p.n_tiles) return;
@@ -149,18 +189,7 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
             uint32_t acc[16];
 #pragma unroll
             for (int i = 0; i < 16; i++) acc[i] = 0;
-#pragma unroll
-            for (int j = 0; j < K; j++) {
-                const uint32_t tj = tl + j * (256 * 32 * 4);
-                const uint32_t w[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
-                    acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
-                    acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
-                    acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
-                }
-            }
+            rs_accumulate<K, FAST>(cur, acc, tl, lane4);
             uint32_t o[4][4];  // o[q][r]
 #pragma unroll
             for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
@@ -242,15 +271,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
     const int own0 = rank ? h0 : 0, n_own = rank ? (p.n_out - h0) : h0;
     const int oth0 = rank ? 0 : h0, n_oth = rank ? h0 : (p.n_out - h0);
 
+    // KH <= 4: fast layout (tables 0..3 single-PRMT addressed in [0x10000,0x30000), exchange buffer +
+    // mbarriers below them); KH = 5, 6 keep the classic contiguous layout (same L1 reason as rs_lut8)
+    constexpr bool FAST = (KH <= 4);
+    const uint32_t s0 = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab));
+    const uint32_t wb = s0 & 0xFF000000u;  // this CTA's window in the cluster shared address space (rank << 24)
+    if (FAST && (s0 - wb) + 128u + RS_X2_XBUF_BYTES + RS_X2_MBAR_BYTES > LUT_BLK_A) __trap();
     for (int e0 = warp * 32; e0 < KH * 256; e0 += NW * 32) {
         const int e = e0 + lane;
         const int j = e >> 8;
         const uint32_t v = (j < ni) ? packed_products(p, j_base + j, static_cast<uint32_t>(e & 255)) : 0u;
 #pragma unroll 8
-        for (int q = 0; q < 32; q++) rs_tab[(e0 + q) * 32 + lane] = __shfl_sync(0xffffffffu, v, q);
+        for (int q = 0; q < 32; q++) {
+            const int eq = e0 + q;
+            const uint32_t addr = FAST ? wb + lut_fast_addr(eq >> 8, static_cast<uint32_t>(eq & 255), lane) : s0 + (eq * 32 + lane) * 4;
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(__shfl_sync(0xffffffffu, v, q)) : "memory");
+        }
     }
-    uint4 *xbuf = reinterpret_cast<uint4 *>(rs_tab + KH * 256 * 32);
-    const uint32_t xbuf_s = static_cast<uint32_t>(__cvta_generic_to_shared(xbuf));
+    const uint32_t xbuf_s = FAST ? ((s0 + 127u) & ~127u) : s0 + KH * 256 * 32 * 4;
+    const uint4 *xbuf = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(rs_tab) + (xbuf_s - s0));
     const uint32_t mbar_s = xbuf_s + RS_X2_XBUF_BYTES;  // full[stage][w] at +(stage*NW+w)*8, empty at +(2*NW + stage*NW+w)*8
     if (threadIdx.x < 4 * NW) mbar_init(mbar_s + threadIdx.x * 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -260,7 +299,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
     const uint32_t my_full = mbar_s + warp * 8, my_empty = mbar_s + (2 * NW + warp) * 8;          // + stage*NW*8
     const uint32_t peer_full = mbar_peer + warp * 8, peer_empty = mbar_peer + (2 * NW + warp) * 8;
 
-    const uint32_t tl = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab)) + lane * 4;
+    const uint32_t tl = s0 + lane * 4;
+    const uint32_t lane4 = wb | static_cast<uint32_t>(lane * 4);
     const unsigned long long n_clusters = gridDim.x >> 1;
     unsigned long long t = blockIdx.x >> 1;
 
@@ -330,18 +370,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
         uint32_t acc[16];
 #pragma unroll
         for (int i = 0; i < 16; i++) acc[i] = 0;
-#pragma unroll
-        for (int j = 0; j < KH; j++) {
-            const uint32_t tj = tl + j * (256 * 32 * 4);
-            const uint32_t w[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
-                acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
-                acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
-                acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
-            }
-        }
+        rs_accumulate<KH, FAST>(cur, acc, tl, lane4);
         uint32_t o[4][4];  // o[q][row]
 #pragma unroll
         for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);

@@ -109,3 +109,26 @@ def scale():
 
 if __name__ == "__main__" and sys.argv[1] == "scale":
     scale()
+
+
+def reco():
+    """reconstruct variants: which kernels do e.g. RS(6,3) 1..3 erasures, RS(4,2), RS(10,4) decode take?"""
+    for k, m, missing in ((6, 3, [1, 4, 7]), (6, 3, [2]), (4, 2, [0, 5]), (10, 4, [0, 3, 11, 13]), (5, 5, [0, 1, 2, 3, 4]), (8, 3, [1, 9])):
+        S = gpu_ec.erasure.shard_len(8 << 20, k)
+        n = 256
+        b = device.StripeBatch(n, k, m, S)
+        b.fill_synthetic(4)
+        b.encode()
+        present = [0 if i in missing else 1 for i in range(k + m)]
+        ms = timed(lambda: b.reconstruct(present), 10)
+        a = (k + len(missing)) * S * n
+        print(f"reconstruct rs({k},{m}) missing={missing}: {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
+        ms = timed(b.encode, 10)
+        a = (k + m) * S * n
+        print(f"encode      rs({k},{m}): {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
+        del b
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__" and sys.argv[1] == "reco":
+    reco()
