@@ -401,7 +401,10 @@ def main():
                 "d2h_bytes_per_step": n_e2e * M_PAR * S, "ms_per_step": round(e2e_ms, 3), "stripes_per_step": n_e2e,
                 "api": "gpu_ec_encode_batch (pinned host buffers)", "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2)},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 1), "peak": peak, "unit": "GB/s", "frac": round(per_gpu / peak, 4),
-                         "traffic": None, "kernel": "rs_lut8_kernel<6>", "peak_source": peak_src,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this shape (64 stripes) from the
+                         # committed ncu --set full capture profiles/r01_final_ncu_full_summary.txt (4.295 GB + 2.117 GB)
+                         "traffic": 6412392000 if n_local == 64 else None, "traffic_unit": "bytes per launch",
+                         "kernel": "rs_lut8_kernel<6>", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes_rank},
             "sub": sub,
         }

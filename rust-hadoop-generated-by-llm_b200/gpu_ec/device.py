@@ -28,7 +28,8 @@ class StripeBatch:
     def __init__(self, n_stripes: int, k: int, m: int, shard_len: int, device="cuda"):
         self.n_stripes, self.k, self.m, self.shard_len = n_stripes, k, m, shard_len
         self.pitch = pitch_of(shard_len)
-        self.buf = torch.zeros((n_stripes, k + m, self.pitch), dtype=torch.uint8, device=device)
+        # uninitialised on purpose: fill_synthetic() writes every byte, encode() every parity byte
+        self.buf = torch.empty((n_stripes, k + m, self.pitch), dtype=torch.uint8, device=device)
 
     def desc(self, first: int = 0, count: int | None = None) -> Stripes:
         count = self.n_stripes - first if count is None else count

@@ -518,3 +518,28 @@ def test_client_ec_write_read_orchestration(L, orc):
     assert np.array_equal(client.read_ec_block("blk", opt, 6, 3, buf.size), buf)
     with pytest.raises(erasure.ErasureError, match="EC block blk unrecoverable: only 5/6 shards available"):
         client.read_ec_block("blk", [None] * 4 + list(plan.shards[4:]), 6, 3, buf.size)
+
+
+def test_two_devices_in_one_process(L, orc):
+    """stripe i -> device i mod G inside the _batch entry points (no collective). Needs >= 2 GPUs."""
+    if L.gpu_ec_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    devs = (C.c_int * 2)(0, 1)
+    _lib.check(L.gpu_ec_set_devices(devs, 2))
+    try:
+        k, m, stripe_len, n = 6, 3, 1 << 20, 10
+        S = erasure.shard_len(stripe_len, k)
+        data = orc.fill_synthetic(stripe_len * n, 0xEC0000D2)
+        parity = np.empty((n, m, S), np.uint8)
+        crcs = np.zeros((n, k + m), np.uint32)
+        _lib.check(L.gpu_ec_encode_batch(data.ctypes.data, stripe_len, n, k, m, parity.ctypes.data, crcs.ctypes.data, None))
+        for i in range(n):
+            want = orc.encode(data[i * stripe_len:(i + 1) * stripe_len], k, m)
+            assert np.array_equal(parity[i], want[k:]), i
+            assert crcs[i].tolist() == [zlib.crc32(s.tobytes()) for s in want]
+        for i in range(4):  # single calls alternate between the devices too
+            d = rnd(70_001 + i, i)
+            assert checksum.crc32(d) == zlib.crc32(d.tobytes())
+    finally:
+        one = (C.c_int * 1)(0)
+        _lib.check(L.gpu_ec_set_devices(one, 1))
