@@ -13,6 +13,12 @@ for p in (ROOT, PKG):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # libgpu_ec.so is a build artefact (git-ignored): compile it when a fresh checkout runs the tests.
+    # nvcc cross-compiles sm_100a without a GPU; on the GPU box the prebuilt library travels with the repo.
+    so = os.path.join(PKG, "libgpu_ec.so")
+    if not os.path.exists(so):
+        import subprocess
+        subprocess.check_call(["make", "-C", os.path.join(PKG, "csrc"), "-s"])
 
 
 @pytest.fixture(scope="session")

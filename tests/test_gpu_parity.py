@@ -235,6 +235,25 @@ def test_crc_chunks_vs_oracle(L, orc, chunk):
                           orc.crc32_chunks(d, chunk, orc.POLY_CASTAGNOLI))
 
 
+def test_crc_whole_multi_gib_three_level_fold(L):
+    """> 2^20 segments in one buffer: the fold runs three levels (1024^2 < segments)."""
+    import torch
+    from gpu_ec import device
+    n = (1 << 29) + 512 * 1025 + 77  # > 2^20 512-byte segments, ragged tail
+    t = torch.empty(n, dtype=torch.uint8, device="cuda")
+    device.fill_synthetic(t, 0xEC0000C3)
+    # force 512-byte segments through the chunk path: 2^20+ chunk CRCs, then compare their fold with the whole CRC
+    chunks = device.crc32_chunks(t, 512)
+    whole = int(device.u32(device.crc32(t))[0])
+    host = t.cpu().numpy()
+    assert whole == zlib.crc32(host.tobytes())
+    ch = device.u32(chunks)
+    for i in (0, 1, 1 << 19, ch.size - 2, ch.size - 1):
+        assert int(ch[i]) == zlib.crc32(host[i * 512:(i + 1) * 512].tobytes())
+    w2, c2 = checksum.block_checksums(host)  # host path: whole CRC folded from 2^20+ chunk CRCs (3 levels)
+    assert w2 == whole and np.array_equal(c2, ch)
+
+
 def test_block_checksums_one_pass(L, orc):
     for n in [61, 512, 513, 65_536, 11_184_811]:
         d = rnd(n, 99 + n)
