@@ -98,7 +98,9 @@ def cpu_reference(steps, warmup, full_line, n_gpus=1):
     ts = [oracle.bench_encode(data, STRIPE_LEN, n_stripes, K_DATA, M_PAR, threads) for _ in range(max(1, steps))]
     t = sum(ts) / len(ts)
     val = alg / t / 1e9
+    t1 = oracle.bench_encode(data, STRIPE_LEN, 1, K_DATA, M_PAR, 1)  # what ONE reference call gets: it is single-threaded
     base = {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": "port",
+            "single_thread_value": round((K_DATA + M_PAR) * S / t1 / 1e9, 3),
             "sample": f"{n_stripes} x 64 MiB RS(6,3) stripes, one stripe per thread, {len(ts)} pass(es); "
                       "C restatement of reed-solomon-erasure 6.0.0 scalar table path incl. erasure.rs:17-20 copies"}
     if not full_line:
@@ -350,6 +352,16 @@ def main():
             sub[f"crc32_ieee_{chunk}B_chunks_1GiB"] = {
                 "write_GBps": round(a2 * world / msw / 1e6, 1), "verify_GBps": round(a2 * world / msv / 1e6, 1),
                 "roofline_frac_write": round(a2 / msw / 1e6 / peak, 4), "roofline_frac_verify": round(a2 / msv / 1e6 / peak, 4)}
+        if world == 1 and not args.no_cpu:  # CPU side of config 2 on a bounded sample (crc32fast's PCLMULQDQ path restated)
+            threads = os.cpu_count() or 1
+            samp = t2[:256 << 20].cpu().numpy()
+            for chunk in (512, 65536):
+                tc = oracle.bench_crc_chunks(samp, chunk, 0, threads)
+                t1c = oracle.bench_crc_chunks(samp[:32 << 20], chunk, 0, 1)
+                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_port_GBps"] = round(samp.size / tc / 1e9, 2)
+                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_port_1thread_GBps"] = round((32 << 20) / t1c / 1e9, 2)
+                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_cores"] = threads
+            del samp
         host_sample = t2[:1 << 20].cpu().numpy()
         chk = device.u32(device.crc32_chunks(t2[:1 << 20], 512))
         if not np.array_equal(chk, oracle.crc32_chunks(host_sample, 512)):

@@ -154,6 +154,27 @@ class BlockStore:
                 bad.append(bid)
         return len(ids), sorted(bad)
 
+    def reconstruct_ec_shard(self, block_id: str, shard_index: int, data_shards: int, parity_shards: int,
+                             fetched: Sequence) -> int:
+        """The byte work of MyChunkServer::reconstruct_ec_shard (chunkserver.rs:503-640) once the peers'
+        shards have been fetched: `fetched[i]` is shard i or None (unavailable source). The target slot is
+        forced to None (:529), at least k others must be present (:607-617), every missing shard is
+        rebuilt (:620-623) and shard `shard_index` is written with its .meta (:626-631). -> bytes written."""
+        from . import erasure
+        total = data_shards + parity_shards
+        if len(fetched) != total:
+            raise ValueError(f"ec_shard_sources length {len(fetched)} != total shards {total}")
+        opt = [None if (i == shard_index or f is None) else _as_u8(f) for i, f in enumerate(fetched)]
+        available = sum(o is not None for o in opt)
+        if available < data_shards:
+            raise ValueError(f"Only {available} shards available, need at least {data_shards} for reconstruction")
+        erasure.reconstruct(opt, data_shards, parity_shards)
+        shard = opt[shard_index]
+        if shard is None:
+            raise ValueError(f"Shard {shard_index} still None after reconstruct")
+        self.write_block(block_id, shard)
+        return int(shard.size)
+
     def write_block(self, block_id: str, data) -> None:
         """write_block_async (chunkserver.rs:192-209): data file + big-endian .meta sidecar."""
         d = _as_u8(data)

@@ -562,3 +562,23 @@ def test_two_devices_in_one_process(L, orc):
     finally:
         one = (C.c_int * 1)(0)
         _lib.check(L.gpu_ec_set_devices(one, 1))
+
+
+def test_reconstruct_ec_shard_repair_path(L, orc, tmp_path):
+    """chunkserver.rs:503-640 after the fetch: rebuild the target shard and store it with its .meta."""
+    store = checksum.BlockStore(str(tmp_path))
+    data = rnd(2_000_003, 11)
+    sh = orc.encode(data, 6, 3)
+    fetched = [s.copy() for s in sh]
+    fetched[2] = None              # unavailable source
+    fetched[7] = None
+    n = store.reconstruct_ec_shard("blk_s4", 4, 6, 3, fetched)   # our own (stale) copy of shard 4 is ignored
+    assert n == sh.shape[1]
+    assert (tmp_path / "blk_s4").read_bytes() == sh[4].tobytes()
+    store.verify_block("blk_s4", sh[4])
+    assert (tmp_path / "blk_s4.meta").read_bytes() == orc.meta_encode_be(orc.crc32_chunks(sh[4]))
+    with pytest.raises(ValueError, match="ec_shard_sources length 8 != total shards 9"):
+        store.reconstruct_ec_shard("x", 0, 6, 3, fetched[:8])
+    fetched[0] = fetched[1] = None  # now only 3, 5, 6, 8 present besides the target
+    with pytest.raises(ValueError, match="Only 4 shards available, need at least 6 for reconstruction"):
+        store.reconstruct_ec_shard("x", 4, 6, 3, fetched)
