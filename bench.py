@@ -114,6 +114,33 @@ def cpu_reference(steps, warmup, full_line, n_gpus=1):
             "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def bind_to_gpu_numa_node(torch, dev):
+    """Run this rank on the CPUs local to its GPU's PCIe root (sysfs local_cpulist), so the pinned
+    staging buffers are first-touched on the NUMA node the DMA engine reads from. Without it the
+    e2e figure at 8 ranks is bounded by the inter-socket link, not by PCIe. Returns a description."""
+    try:
+        pr = torch.cuda.get_device_properties(dev)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open(f"/sys/bus/pci/devices/{bdf}/local_cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+                node = f.read().strip()
+            return f"gpu {bdf}: numa node {node}, {len(cpus)} local cpus"
+    except Exception as e:  # noqa: BLE001
+        return f"not bound ({type(e).__name__})"
+    return "not bound"
+
+
 def run_e2e(L, oracle, np, C, check, barrier, partition, dist, world, rank, S, n_e2e):
     hin, hout = C.c_void_p(), C.c_void_p()
     check(L.gpu_ec_alloc_pinned(C.byref(hin), n_e2e * STRIPE_LEN))
@@ -248,6 +275,7 @@ def main():
 
     warmup = max(3, args.warmup)
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(torch, local)  # before any pinned allocation: first touch decides the node
     if world > 1:
         # bookkeeping only (barrier, max elapsed): stripes are independent, so the data path has no
         # collective and NCCL/NVLink stay unused by design; gloo keeps stdout to the one JSON line
@@ -411,7 +439,7 @@ def main():
             "e2e": None if e2e_val is None else {
                 "value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": n_e2e * STRIPE_LEN,
                 "d2h_bytes_per_step": n_e2e * M_PAR * S, "ms_per_step": round(e2e_ms, 3), "stripes_per_step": n_e2e,
-                "api": "gpu_ec_encode_batch (pinned host buffers)", "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2)},
+                "api": "gpu_ec_encode_batch (pinned host buffers)", "host_binding": numa, "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2)},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 1), "peak": peak, "unit": "GB/s", "frac": round(per_gpu / peak, 4),
                          # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this shape (64 stripes) from the
                          # committed ncu --set full capture profiles/r01_final_ncu_full_summary.txt (4.295 GB + 2.117 GB)
