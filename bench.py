@@ -425,6 +425,22 @@ def main():
         del b4
         torch.cuda.empty_cache()
         sub["e2e_32_streams_256MiB_blocks"] = run_config5(L, oracle, np, C, check, rank)
+        # small calls: there is no CPU fallback, so a 28-byte encode also goes to the GPU;
+        # this is the price in latency, reported so nobody has to guess it
+        from gpu_ec import checksum as _ck, erasure as _er
+        small = {}
+        for name, fn in (("encode_28B_rs42", lambda: _er.encode(b"Hello, Erasure Coding World!", 4, 2)),
+                         ("encode_1MiB_rs63", lambda: _er.encode(src_1m, 6, 3)),
+                         ("crc32_64KiB", lambda: _ck.crc32(src_1m[:65536])),
+                         ("calculate_checksums_1MiB", lambda: _ck.calculate_checksums(src_1m))):
+            src_1m = oracle.fill_synthetic(1 << 20, 7)
+            for _ in range(5):
+                fn()
+            t0 = time.perf_counter()
+            for _ in range(50):
+                fn()
+            small[name] = round((time.perf_counter() - t0) / 50 * 1e6, 1)
+        sub["small_call_latency_us"] = dict(small, note="host-pointer API incl. pageable H2D/D2H and Python ctypes overhead")
 
     if rank == 0:
         line = {

@@ -391,6 +391,19 @@ def test_dev_crc_chunks_and_verify(L, orc):
     assert int(device.verify_chunks(t, 512, meta_u8).item()) == 10_000_000 // 512
 
 
+def test_dev_crc_unaligned_views(L, orc):
+    """Device buffers that are not 16-byte aligned take the generic (still CUDA) kernel."""
+    import torch
+    from gpu_ec import device
+    t = torch.empty(300_000, dtype=torch.uint8, device="cuda")
+    device.fill_synthetic(t, 0xEC0000A1)
+    host = t.cpu().numpy()
+    for off in (1, 3, 8, 15):
+        v = t[off:off + 200_001]
+        assert int(device.u32(device.crc32(v))[0]) == zlib.crc32(host[off:off + 200_001].tobytes())
+        assert np.array_equal(device.u32(device.crc32_chunks(v, 512)), orc.crc32_chunks(host[off:off + 200_001], 512))
+
+
 def test_linearity_and_checksum_of_checksums_full_size(L):
     """Size-independent properties at BASELINE sizes (no oracle pass over the whole input)."""
     import torch
