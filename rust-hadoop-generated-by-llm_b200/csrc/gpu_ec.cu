@@ -266,7 +266,7 @@ template <int KH>
 static cudaError_t launch_x2(const RsParams &p, int n_clusters, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * n_clusters);
-    cfg.blockDim = dim3(RS_THREADS);
+    cfg.blockDim = dim3(RS_X2_THREADS);
     cfg.dynamicSmemBytes = x2_smem_bytes(KH);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -285,7 +285,7 @@ static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows,
     p.shard_stride = s.shard_stride;
     p.stripe_stride = s.stripe_stride;
     p.nvec = static_cast<unsigned int>(div_up(s.shard_len, 16));
-    p.tiles_per_stripe = static_cast<unsigned int>(div_up(p.nvec, RS_THREADS));
+    p.tiles_per_stripe = static_cast<unsigned int>(div_up(p.nvec, RS_X2_THREADS));
     p.n_tiles = static_cast<unsigned long long>(s.n_stripes) * p.tiles_per_stripe;
     p.n_in = ni;
     p.n_out = no;

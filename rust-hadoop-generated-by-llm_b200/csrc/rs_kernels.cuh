@@ -227,8 +227,12 @@ __global__ void __launch_bounds__(RS_THREADS, 1) rs_lut8_kernel(const __grid_con
 // and halves throughput). HBM traffic stays algorithmic: every input byte read once, every output
 // byte written once; DSMEM carries ~0.4 B per input byte.
 constexpr int RS_X2_MAX_KH = 6;  // 6 * 32 KiB tables + 32 KiB exchange + mbarriers <= 227 KiB
-constexpr int RS_X2_NW = RS_THREADS / 32;
-constexpr int RS_X2_XBUF_BYTES = 2 * 2 * RS_THREADS * 16;      // [2 stages][2 rows][RS_THREADS] uint4
+#ifndef GPU_EC_X2_THREADS
+#define GPU_EC_X2_THREADS 512
+#endif
+constexpr int RS_X2_THREADS = GPU_EC_X2_THREADS;
+constexpr int RS_X2_NW = RS_X2_THREADS / 32;
+constexpr int RS_X2_XBUF_BYTES = 2 * 2 * RS_X2_THREADS * 16;   // [2 stages][2 rows][RS_X2_THREADS] uint4
 constexpr int RS_X2_MBAR_BYTES = 2 * 2 * RS_X2_NW * 8;         // full[2][NW], empty[2][NW]
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
@@ -259,7 +263,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t a, uint32_t parity) {
 }
 
 template <int KH>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lut8x2_kernel(const __grid_constant__ RsParams p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_X2_THREADS, 1) rs_lut8x2_kernel(const __grid_constant__ RsParams p) {
     extern __shared__ __align__(16) uint32_t rs_tab[];  // tables | exchange buffer | mbarriers
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -320,7 +324,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
 
     uint4 cur[KH];
     auto locate_next = [&](unsigned long long &off) -> bool {   // locate (nstripe, ntt), then advance by one step
-        const unsigned int v = ntt * RS_THREADS + threadIdx.x;
+        const unsigned int v = ntt * RS_X2_THREADS + threadIdx.x;
         off = nstripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
         nstripe += step_stripe;
         ntt += step_tt;
@@ -346,9 +350,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
         const unsigned int ps_ = (it - 1) & 1u, pu_ = (it - 1) >> 1;                                                 \
         if (n_own > 0) {                                                                                             \
             mbar_wait(my_full + ps_ * (NW * 8), pu_ & 1u);                                                           \
-            const uint4 *x = xbuf + ps_ * (2 * RS_THREADS) + threadIdx.x;                                            \
+            const uint4 *x = xbuf + ps_ * (2 * RS_X2_THREADS) + threadIdx.x;                                            \
             uint4 o0_ = x[0], o1_ = make_uint4(0, 0, 0, 0);                                                          \
-            if (n_own > 1) o1_ = x[RS_THREADS];                                                                      \
+            if (n_own > 1) o1_ = x[RS_X2_THREADS];                                                                      \
             o0_.x ^= keep0.x; o0_.y ^= keep0.y; o0_.z ^= keep0.z; o0_.w ^= keep0.w;                                  \
             o1_.x ^= keep1.x; o1_.y ^= keep1.y; o1_.z ^= keep1.z; o1_.w ^= keep1.w;                                  \
             __syncwarp();                                                                                            \
@@ -381,7 +385,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
         // the partner's warp must have drained this stage's previous use (first use passes at once)
         if (n_oth > 0) mbar_wait(my_empty + st_ * (NW * 8), (use_ & 1u) ^ 1u);
         // rows the partner finishes go into its exchange buffer, rows we finish wait in registers
-        const uint32_t dst = xbuf_peer + (st_ * (2 * RS_THREADS) + threadIdx.x) * 16u;
+        const uint32_t dst = xbuf_peer + (st_ * (2 * RS_X2_THREADS) + threadIdx.x) * 16u;
         const uint32_t sig = peer_full + st_ * (NW * 8);
         uint4 own_a, own_b;
         if (p.n_out == RS_MAX_OUT) {  // the common 4-row case: rows are compile-time per rank
@@ -389,7 +393,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
             const uint4 r2 = make_uint4(o[0][2], o[1][2], o[2][2], o[3][2]), r3 = make_uint4(o[0][3], o[1][3], o[2][3], o[3][3]);
             const bool hi = rank != 0;
             st_async_peer(dst, hi ? r0 : r2, sig);
-            st_async_peer(dst + RS_THREADS * 16, hi ? r1 : r3, sig);
+            st_async_peer(dst + RS_X2_THREADS * 16, hi ? r1 : r3, sig);
             own_a = hi ? r2 : r0;
             own_b = hi ? r3 : r1;
         } else {
@@ -398,7 +402,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_THREADS, 1) rs_lu
             for (int row = 0; row < RS_MAX_OUT; row++) {
                 const uint4 v = make_uint4(o[0][row], o[1][row], o[2][row], o[3][row]);
                 if (n_oth > 0 && row == oth0) st_async_peer(dst, v, sig);
-                if (n_oth > 1 && row == oth0 + 1) st_async_peer(dst + RS_THREADS * 16, v, sig);
+                if (n_oth > 1 && row == oth0 + 1) st_async_peer(dst + RS_X2_THREADS * 16, v, sig);
                 if (n_own > 0 && row == own0) own_a = v;
                 if (n_own > 1 && row == own0 + 1) own_b = v;
             }
