@@ -89,6 +89,12 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
  * slot (data and parity) in place; shards[i] must point at shard_len writable bytes for absent
  * slots too. present[i] != 0 marks a surviving shard. */
 int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m);
+/* The repair path's variant (chunkserver.rs:503-640 keeps only opt_shards[shard_index] of what
+ * reconstruct rebuilt): rebuild ONLY the absent slots listed in want[n_want] (one pass over the first
+ * k present shards, n_want outputs); other absent slots are left untouched. Same errors as
+ * gpu_ec_reconstruct; a wanted slot that is present or out of range is GPU_EC_ERR_INVALID_ARG. */
+int gpu_ec_reconstruct_only(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m,
+                            const int *want, int n_want);
 /* erasure.rs:30-49 decode(): reconstruct, then concatenate shards[0..k) truncated to original_len.
  * `present` is updated (all ones on success), mirroring the in-place Option fill. */
 int gpu_ec_decode(uint8_t *const *shards, uint8_t *present, size_t shard_len, int k, int m,

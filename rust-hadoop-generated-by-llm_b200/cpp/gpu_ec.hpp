@@ -120,6 +120,25 @@ inline void reconstruct(OptShards &shards, size_t k, size_t m) {
         if (!shards[i]) shards[i] = std::move(fresh[i]);
 }
 
+/// the repair path's variant: rebuild only the listed missing slots (chunkserver.rs:626-631 keeps one)
+inline void reconstruct_only(OptShards &shards, size_t k, size_t m, const std::vector<int> &want) {
+    if (k == 0 || m == 0) throw Error(GPU_EC_ERR_ZERO_SHARDS, gpu_ec_strerror(GPU_EC_ERR_ZERO_SHARDS));
+    if (shards.size() != k + m) throw Error(GPU_EC_ERR_INVALID_ARG, "RS reconstruct error: TooFewShards");
+    size_t s = 0;
+    for (auto &o : shards) if (o) s = o->size();
+    std::vector<uint8_t> present(shards.size());
+    std::vector<Bytes> fresh(shards.size());
+    std::vector<uint8_t *> ptrs(shards.size());
+    for (size_t i = 0; i < shards.size(); i++) {
+        present[i] = shards[i] ? 1 : 0;
+        if (shards[i]) ptrs[i] = shards[i]->data();
+        else { fresh[i].assign(s, 0); ptrs[i] = fresh[i].data(); }
+    }
+    check(gpu_ec_reconstruct_only(ptrs.data(), present.data(), s, static_cast<int>(k), static_cast<int>(m), want.data(),
+                                  static_cast<int>(want.size())));
+    for (int i : want) shards[static_cast<size_t>(i)] = std::move(fresh[static_cast<size_t>(i)]);
+}
+
 /// dfs/common/src/erasure.rs:30
 inline Bytes decode(OptShards &shards, size_t k, size_t m, size_t original_len) {
     reconstruct(shards, k, m);

@@ -946,6 +946,44 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
     return GPU_EC_OK;
 }
 
+int gpu_ec_reconstruct_only(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m,
+                            const int *want, int n_want) {
+    if (!shards || !present || !want || n_want <= 0) return GPU_EC_ERR_INVALID_ARG;
+    DecodePlan plan;
+    bool noop = false;
+    RET(reconstruct_plan(k, m, present, plan, noop));
+    const int n = k + m;
+    for (int i = 0; i < n_want; i++)
+        if (want[i] < 0 || want[i] >= n || present[want[i]] || !shards[want[i]]) return GPU_EC_ERR_INVALID_ARG;
+    if (shard_len == 0) return GPU_EC_ERR_EMPTY_SHARD;
+    // the decode rows of just the wanted slots, in the caller's order
+    std::vector<uint8_t> rows(static_cast<size_t>(n_want) * k);
+    std::vector<int> outs(n_want);
+    for (int i = 0; i < n_want; i++) {
+        const auto it = std::find(plan.missing.begin(), plan.missing.end(), want[i]);
+        if (it == plan.missing.end()) return GPU_EC_ERR_INVALID_ARG;
+        memcpy(&rows[static_cast<size_t>(i) * k], &plan.rows[static_cast<size_t>(it - plan.missing.begin()) * k], k);
+        outs[i] = want[i];
+    }
+    const size_t S = shard_len, pitch = round_up(S, 256);
+    Lease L;
+    RET(lease_any(L));
+    RET(slot_reserve(*L.s, static_cast<size_t>(n) * pitch));
+    cudaStream_t st = L.s->stream;
+    uint8_t *db = L.s->dbuf;
+    for (int j = 0; j < k; j++) {
+        const int idx = plan.survivors[j];
+        if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
+        CK(cudaMemcpyAsync(db + static_cast<size_t>(idx) * pitch, shards[idx], S, cudaMemcpyHostToDevice, st));
+    }
+    gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
+    RET(launch_apply(*L.d, sv, rows.data(), plan.survivors.data(), k, outs.data(), n_want, st));
+    for (int i = 0; i < n_want; i++)
+        CK(cudaMemcpyAsync(shards[want[i]], db + static_cast<size_t>(want[i]) * pitch, S, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return GPU_EC_OK;
+}
+
 int gpu_ec_decode(uint8_t *const *shards, uint8_t *present, size_t shard_len, int k, int m, size_t original_len,
                   uint8_t *out) {
     if (!shards || !present || (!out && original_len)) return GPU_EC_ERR_INVALID_ARG;

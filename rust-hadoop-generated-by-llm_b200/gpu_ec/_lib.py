@@ -76,6 +76,7 @@ SIGNATURES = {
     "gpu_ec_crc32_combine": (_u32, [_u32, _u32, _sz, _i]),
     "gpu_ec_encode": (_i, [_vp, _sz, _i, _i, _vp, _vp, _vp, _vp]),
     "gpu_ec_reconstruct": (_i, [_vp, _vp, _sz, _i, _i]),
+    "gpu_ec_reconstruct_only": (_i, [_vp, _vp, _sz, _i, _i, _vp, _i]),
     "gpu_ec_decode": (_i, [_vp, _vp, _sz, _i, _i, _sz, _vp]),
     "gpu_ec_crc32": (_i, [_vp, _sz, _i, _vp]),
     "gpu_ec_crc32_chunks": (_i, [_vp, _sz, _sz, _i, _vp]),

@@ -168,7 +168,8 @@ class BlockStore:
         available = sum(o is not None for o in opt)
         if available < data_shards:
             raise ValueError(f"Only {available} shards available, need at least {data_shards} for reconstruction")
-        erasure.reconstruct(opt, data_shards, parity_shards)
+        # the reference rebuilds every missing shard and keeps one; only the kept one is computed here
+        erasure.reconstruct_only(opt, data_shards, parity_shards, [shard_index])
         shard = opt[shard_index]
         if shard is None:
             raise ValueError(f"Shard {shard_index} still None after reconstruct")

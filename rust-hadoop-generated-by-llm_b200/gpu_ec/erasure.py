@@ -114,6 +114,20 @@ def reconstruct(shards: List[Optional[np.ndarray]], data_shards: int, parity_sha
 
 
 @_wrap
+def reconstruct_only(shards: List[Optional[np.ndarray]], data_shards: int, parity_shards: int, want: Sequence[int]) -> None:
+    """Rebuild only the listed missing slots (the repair path keeps one shard, chunkserver.rs:626-631);
+    other None slots stay None."""
+    n = data_shards + parity_shards
+    if data_shards <= 0 or parity_shards <= 0:
+        raise GpuEcError(ERR_ZERO_SHARDS)
+    present, S, bufs = _prepare(shards, n)
+    w = (C.c_int * len(want))(*want)
+    check(lib().gpu_ec_reconstruct_only(_ptr_array(bufs), present.ctypes.data, S, data_shards, parity_shards, w, len(want)))
+    for i in want:
+        shards[i] = bufs[i]
+
+
+@_wrap
 def decode(shards: List[Optional[np.ndarray]], data_shards: int, parity_shards: int, original_len: int) -> np.ndarray:
     """erasure.rs:30-49."""
     n = data_shards + parity_shards

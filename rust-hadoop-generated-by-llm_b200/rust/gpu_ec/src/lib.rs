@@ -20,6 +20,11 @@ mod ffi {
         pub fn gpu_ec_encode(data: *const u8, len: usize, k: c_int, m: c_int, shards_out: *const *mut u8,
                              shard_crc_out: *mut u32, full_crc_out: *mut u32, meta_out: *const *mut u8) -> c_int;
         pub fn gpu_ec_reconstruct(shards: *const *mut u8, present: *const u8, shard_len: usize, k: c_int, m: c_int) -> c_int;
+        pub fn gpu_ec_reconstruct_only(shards: *const *mut u8, present: *const u8, shard_len: usize, k: c_int, m: c_int,
+                                       want: *const c_int, n_want: c_int) -> c_int;
+        pub fn gpu_ec_verify_chunks_batch(n_blocks: usize, data: *const *const u8, lens: *const usize, chunk: usize, poly: c_int,
+                                          meta_be: *const *const u8, meta_lens: *const usize, status_out: *mut c_int,
+                                          first_bad_out: *mut i64) -> c_int;
         pub fn gpu_ec_crc32(data: *const u8, len: usize, poly: c_int, out: *mut u32) -> c_int;
         pub fn gpu_ec_crc32_chunks(data: *const u8, len: usize, chunk: usize, poly: c_int, out: *mut u32) -> c_int;
         pub fn gpu_ec_verify_chunks(data: *const u8, len: usize, chunk: usize, poly: c_int, meta_be: *const u8,
@@ -94,6 +99,50 @@ pub fn reconstruct(shards: &mut [Option<Vec<u8>>], k: usize, m: usize) -> Result
         return Err(anyhow!("{}", msg(rc)));
     }
     Ok(())
+}
+
+/// The repair path (chunkserver.rs:503-640) keeps only `opt_shards[shard_index]`: rebuild just that slot.
+pub fn reconstruct_one(shards: &mut [Option<Vec<u8>>], k: usize, m: usize, shard_index: usize) -> Result<()> {
+    if shards.len() != k + m { bail!("ec_shard_sources length {} != total shards {}", shards.len(), k + m); }
+    shards[shard_index] = None; // chunkserver.rs:529
+    let available = shards.iter().filter(|s| s.is_some()).count();
+    if available < k { bail!("Only {} shards available, need at least {} for reconstruction", available, k); }
+    let s = shards.iter().flatten().map(|v| v.len()).next().unwrap_or(0);
+    let present: Vec<u8> = shards.iter().map(|o| o.is_some() as u8).collect();
+    let mut target = vec![0u8; s];
+    let mut dummy = vec![0u8; 0];
+    let ptrs: Vec<*mut u8> = shards.iter_mut().enumerate().map(|(i, o)| match o {
+        Some(v) => v.as_mut_ptr(),
+        None if i == shard_index => target.as_mut_ptr(),
+        None => dummy.as_mut_ptr(),
+    }).collect();
+    let want = [shard_index as c_int];
+    let rc = unsafe { ffi::gpu_ec_reconstruct_only(ptrs.as_ptr(), present.as_ptr(), s, k as c_int, m as c_int, want.as_ptr(), 1) };
+    if rc != 0 { return Err(anyhow!("{}", msg(rc))); }
+    shards[shard_index] = Some(target);
+    Ok(())
+}
+
+/// One pass of run_background_scrubber (chunkserver.rs:652-701) as ONE batched verify.
+/// Returns, per block, Ok(()) or the same Err text verify_block gives.
+pub fn verify_blocks(blocks: &[&[u8]], metas: &[&[u8]]) -> Vec<std::result::Result<(), String>> {
+    let n = blocks.len();
+    let dp: Vec<*const u8> = blocks.iter().map(|b| b.as_ptr()).collect();
+    let dl: Vec<usize> = blocks.iter().map(|b| b.len()).collect();
+    let mp: Vec<*const u8> = metas.iter().map(|b| b.as_ptr()).collect();
+    let ml: Vec<usize> = metas.iter().map(|b| b.len()).collect();
+    let mut st = vec![0 as c_int; n];
+    let mut bad = vec![-1i64; n];
+    let rc = unsafe {
+        ffi::gpu_ec_verify_chunks_batch(n, dp.as_ptr(), dl.as_ptr(), CHECKSUM_CHUNK_SIZE, 0, mp.as_ptr(), ml.as_ptr(),
+                                        st.as_mut_ptr(), bad.as_mut_ptr())
+    };
+    (0..n).map(|i| match if rc != 0 { rc } else { st[i] } {
+        0 => Ok(()),
+        ERR_COUNT_MISMATCH => Err("Checksum count mismatch".to_string()),
+        ERR_CRC_MISMATCH => Err(format!("Checksum mismatch at chunk {}", bad[i])),
+        other => Err(msg(other)),
+    }).collect()
 }
 
 /// dfs/common/src/erasure.rs:30

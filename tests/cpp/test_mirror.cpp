@@ -65,6 +65,17 @@ int main(int argc, char **argv) {
         erasure::reconstruct(opt, 4, 2);
         REQUIRE(*opt[4] == shards[4]);
     }
+    // repair path: only the wanted shard is rebuilt, the other missing slot stays empty
+    {
+        Bytes data(100003);
+        for (size_t i = 0; i < data.size(); i++) data[i] = static_cast<uint8_t>(i * 7 + 3);
+        auto shards = erasure::encode(data, 6, 3);
+        auto opt = some(shards);
+        opt[1].reset();
+        opt[7].reset();
+        erasure::reconstruct_only(opt, 6, 3, {7});
+        REQUIRE(opt[7] && *opt[7] == shards[7] && !opt[1]);
+    }
     // client/src/mod.rs:1541-1551: 1024 B at RS(4,2) -> 6 shards of 256 B
     {
         auto shards = erasure::encode(Bytes(1024, 0), 4, 2);

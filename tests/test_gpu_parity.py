@@ -595,3 +595,20 @@ def test_reconstruct_ec_shard_repair_path(L, orc, tmp_path):
     fetched[0] = fetched[1] = None  # now only 3, 5, 6, 8 present besides the target
     with pytest.raises(ValueError, match="Only 4 shards available, need at least 6 for reconstruction"):
         store.reconstruct_ec_shard("x", 4, 6, 3, fetched)
+
+
+def test_reconstruct_only_wanted_slots(L, orc):
+    data = rnd(500_003, 3)
+    for k, m, missing, want in [(6, 3, [1, 4, 7], [4]), (6, 3, [0, 8], [8, 0]), (10, 4, [2, 5, 11, 13], [13, 2]), (4, 2, [3], [3])]:
+        sh = orc.encode(data, k, m)
+        opt = [None if i in missing else sh[i].copy() for i in range(k + m)]
+        erasure.reconstruct_only(opt, k, m, want)
+        for i in range(k + m):
+            if i in want:
+                assert np.array_equal(opt[i], sh[i]), (k, m, i)
+            elif i in missing:
+                assert opt[i] is None
+    opt = [s.copy() for s in orc.encode(data, 6, 3)]
+    opt[2] = None
+    with pytest.raises(erasure.ErasureError, match="invalid argument"):
+        erasure.reconstruct_only(opt, 6, 3, [3])  # slot 3 is present
