@@ -13,9 +13,13 @@
 //     shard whose u32 entry packs the products for all 4 output rows; the table is replicated
 //     per lane (word index = entry*32 + lane) so every LDS is bank-conflict-free. 32 KiB per
 //     input shard -> n_in <= 7 in the 227 KiB of one SM.
+//   * rs_lut8x2: the same for 8 <= n_in <= 12 (RS(10,4)) on a 2-CTA thread-block cluster: the SM
+//     pair splits the tables and trades partial parity over distributed shared memory.
 //   * rs_lut4: split-nibble variant (two 16-entry packed tables per input shard, 4 KiB per
-//     shard, lane-replicated, 2 lookups per byte) for n_in up to 56 per pass, with an
-//     accumulate flag so wider codes (k+m <= 256) are covered in several passes.
+//     shard, lane-replicated, 2 lookups per byte) for very wide codes, n_in up to 56 per pass,
+//     with an accumulate flag so k+m <= 256 is covered in several passes.
+//   * where the tables fit below 192 KiB in 64 KiB-aligned blocks (n_in <= 5, cluster KH <= 4) a
+//     lookup is PRMT + LDS (lut_common.cuh); otherwise PRMT/SHF + IMAD + LDS.
 //   * 16-byte coalesced loads straight into registers (no reuse -> no smem staging needed),
 //     next tile prefetched before the current one is computed, XOR-accumulate in registers,
 //     4x4 byte transpose with PRMT, 16-byte coalesced stores: each byte crosses HBM once.
