@@ -318,8 +318,13 @@ __global__ void crc_fold_kernel(const __grid_constant__ FoldParams p) {
     const unsigned int team = threadIdx.x / T, tau = threadIdx.x - team * T;
     const unsigned int lane = tau & 31, wteam = tau >> 5, gwarp = threadIdx.x >> 5;
     const uint32_t P = p.poly_bits;
-    const uint32_t my_c1 = p.c1[lane];
-    const uint32_t my_c2 = p.c2[lane];
+    // per-lane constants through shared memory: a lane-indexed read of the parameter bank would be
+    // replayed 32 times per warp, and most threads fold exactly one element
+    __shared__ uint32_t cc[64];
+    if (threadIdx.x < 64) cc[threadIdx.x] = (threadIdx.x < 32) ? p.c1[threadIdx.x] : p.c2[threadIdx.x - 32];
+    __syncthreads();
+    const uint32_t my_c1 = cc[lane];
+    const uint32_t my_c2 = cc[32 + lane];
     const unsigned long long total = p.n_buf * p.outs_per_buf * p.nb;
     for (unsigned long long item0 = static_cast<unsigned long long>(blockIdx.x) * tpc; item0 < total;
          item0 += static_cast<unsigned long long>(gridDim.x) * tpc) {
