@@ -71,13 +71,12 @@ struct CrcParams {
 
 __device__ __forceinline__ uint32_t bswap32(uint32_t v) { return __byte_perm(v, 0, 0x0123); }
 
-__device__ __forceinline__ void crc_emit(const CrcParams &p, unsigned long long buf, unsigned long long seg, uint32_t crc) {
+// `want` = the stored big-endian word of this segment, read as a little-endian u32; in verify mode
+// the kernel loads it when it ENTERS the segment so the compare at the end never waits on memory
+__device__ __forceinline__ void crc_emit(const CrcParams &p, unsigned long long buf, unsigned long long seg, uint32_t crc, uint32_t want) {
     const uint32_t stored = p.big_endian ? bswap32(crc) : crc;
     if (p.out) p.out[buf * p.out_stride + seg] = stored;
-    if (p.expect_be) {
-        const uint32_t want = *reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * seg);  // BE bytes read as LE word
-        if (want != bswap32(crc)) atomicMin(p.first_bad, seg);
-    }
+    if (p.expect_be && want != bswap32(crc)) atomicMin(p.first_bad, seg);
 }
 
 __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __grid_constant__ CrcParams p) {
@@ -185,7 +184,7 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
     // a tile whose only row is a short ragged segment may have zero full slices: still one pass
     const unsigned int ncol_loop = ncol ? ncol : 1u;
     if (tile < n_tiles) { enter_tile(t_buf, t_til); issue_loads(0); }
-    uint32_t c = 0xFFFFFFFFu;
+    uint32_t c = 0xFFFFFFFFu, want = 0;
     while (tile < n_tiles) {
         wait_loads();
         __syncwarp();
@@ -208,6 +207,8 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
             col++;
         }
         if (tile < n_tiles) issue_loads(col);
+        if (cur_col == 0 && p.expect_be && seg < p.segs_per_buf)
+            want = __ldg(reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * seg));
         if (cur_col < cols_of(seg)) {
 #pragma unroll
             for (int q = 0; q < 8; q++) {
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
         }
         if (last_col) {
             if (seg < p.nfull) {
-                crc_emit(p, buf, seg, ~c);
+                crc_emit(p, buf, seg, ~c, want);
             } else if (seg == p.nfull && p.rag) {
                 // the ragged segment: its last (rag % 128) bytes straight from global
                 const uint8_t *src = p.base + buf * p.buf_stride + p.nfull * p.G + (static_cast<unsigned long long>(ncol_rag) << 7);
@@ -227,7 +228,7 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
                 unsigned int i = 0;
                 for (; i + 4 <= left; i += 4) c = step_word(c, *reinterpret_cast<const uint32_t *>(src + i));
                 for (; i < left; i++) c = (c >> 8) ^ CRC_LUT(lb_b, 1, c ^ src[i], 0);
-                crc_emit(p, buf, seg, ~c);
+                crc_emit(p, buf, seg, ~c, want);
             }
             c = 0xFFFFFFFFu;
         }

@@ -132,3 +132,19 @@ def reco():
 
 if __name__ == "__main__" and sys.argv[1] == "reco":
     reco()
+
+
+def verify():
+    n = 1 << 30
+    t = torch.empty(n, dtype=torch.uint8, device="cuda")
+    device.fill_synthetic(t, 2)
+    for chunk in (512, 65536):
+        out = torch.empty(n // chunk, dtype=torch.int32, device="cuda")
+        device.crc32_chunks(t, chunk, out=out, big_endian=True)
+        bad = torch.empty(1, dtype=torch.int64, device="cuda")
+        ms = timed(lambda: device.verify_chunks(t, chunk, out.view(torch.uint8), out=bad))
+        print(f"verify chunk={chunk}: {n/ms/1e6:.0f} GB/s frac={n/ms/1e6/PEAK:.3f} bad={int(bad.item())}")
+
+
+if __name__ == "__main__" and sys.argv[1] == "verify":
+    verify()
