@@ -217,6 +217,7 @@ static int check_stripes(const gpu_ec_stripes *s) {
     if (!s || !s->base) return GPU_EC_ERR_INVALID_ARG;
     if ((reinterpret_cast<uintptr_t>(s->base) & 15) || (s->shard_stride & 15) || (s->stripe_stride & 15)) return GPU_EC_ERR_UNALIGNED;
     if (s->shard_stride < round_up(s->shard_len, 16)) return GPU_EC_ERR_INVALID_ARG;
+    if (s->shard_stride / 16 * 256 >= (1ull << 32)) return GPU_EC_ERR_INVALID_ARG;  // slot offsets are 32-bit vector indices
     return GPU_EC_OK;
 }
 
@@ -239,8 +240,8 @@ static int launch_apply_pass(Dev &d, const gpu_ec_stripes &s, const uint8_t *row
     p.n_in = ni;
     p.n_out = no;
     p.accumulate = accumulate ? 1 : 0;
-    for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[r];
-    for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j];
+    for (int r = 0; r < no; r++) { p.out_idx[r] = out_idx[r]; p.out_off16[r] = static_cast<unsigned int>(out_idx[r] * (s.shard_stride / 16)); }
+    for (int j = 0; j < ni; j++) { p.in_idx[j] = in_idx[j]; p.in_off16[j] = static_cast<unsigned int>(in_idx[j] * (s.shard_stride / 16)); }
     for (int r = 0; r < no; r++)
         for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * row_stride + j];
     const int grid = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count)));
@@ -289,8 +290,8 @@ static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows,
     p.n_tiles = static_cast<unsigned long long>(s.n_stripes) * p.tiles_per_stripe;
     p.n_in = ni;
     p.n_out = no;
-    for (int r = 0; r < no; r++) p.out_idx[r] = out_idx[r];
-    for (int j = 0; j < ni; j++) p.in_idx[j] = in_idx[j];
+    for (int r = 0; r < no; r++) { p.out_idx[r] = out_idx[r]; p.out_off16[r] = static_cast<unsigned int>(out_idx[r] * (s.shard_stride / 16)); }
+    for (int j = 0; j < ni; j++) { p.in_idx[j] = in_idx[j]; p.in_off16[j] = static_cast<unsigned int>(in_idx[j] * (s.shard_stride / 16)); }
     for (int r = 0; r < no; r++)
         for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * row_stride + j];
     const int n_clusters = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count / 2)));
