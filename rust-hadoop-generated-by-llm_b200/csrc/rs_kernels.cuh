@@ -319,41 +319,44 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_X2_THREADS, 1) rs
     const unsigned long long n_clusters = gridDim.x >> 1;
     unsigned long long t = blockIdx.x >> 1;
 
-    // loop-invariant addressing: per-input and per-owned-row byte offsets, and the (stripe, tile in
-    // stripe) pair advanced incrementally so the loop has no division and no 64-bit index math
-    const uint8_t *in_ptr[KH];
-#pragma unroll
-    for (int j = 0; j < KH; j++)
-        in_ptr[j] = p.base + static_cast<unsigned long long>(p.in_idx[(j < ni) ? (j_base + j) : j_base]) * p.shard_stride;
-    uint8_t *out_ptr0 = p.base + static_cast<unsigned long long>(p.out_idx[n_own > 0 ? own0 : 0]) * p.shard_stride;
-    uint8_t *out_ptr1 = p.base + static_cast<unsigned long long>(p.out_idx[n_own > 1 ? own0 + 1 : 0]) * p.shard_stride;
+    // Loop-invariant addressing as in rs_lut8: slot offsets are host-precomputed 32-bit vector indices,
+    // the tile position is (stripe pointer, vector index) advanced incrementally, loads are
+    // unconditional (a thread past the end re-reads the last vector; its result is never stored).
     const unsigned int tps = p.tiles_per_stripe;
     const unsigned long long step_stripe = n_clusters / tps;
     const unsigned int step_tt = static_cast<unsigned int>(n_clusters - step_stripe * tps);
-    unsigned long long nstripe = t / tps;                       // position of the NEXT tile to locate
-    unsigned int ntt = static_cast<unsigned int>(t - nstripe * tps);
-
-    uint4 cur[KH];
-    auto locate_next = [&](unsigned long long &off) -> bool {   // locate (nstripe, ntt), then advance by one step
-        const unsigned int v = ntt * RS_X2_THREADS + threadIdx.x;
-        off = nstripe * p.stripe_stride + static_cast<unsigned long long>(v) * 16ull;
-        nstripe += step_stripe;
-        ntt += step_tt;
-        if (ntt >= tps) { ntt -= tps; nstripe++; }
-        return v < p.nvec;
-    };
-    auto load = [&](uint4 (&d)[KH], unsigned long long off, bool ok) {
+    const unsigned long long d_sbase = step_stripe * p.stripe_stride;
+    unsigned long long sbase = (t / tps) * p.stripe_stride;
+    unsigned int ntt = static_cast<unsigned int>(t % tps);
+    const unsigned int last_vec = p.nvec - 1;
+    const unsigned int own_off0 = p.out_off16[n_own > 0 ? own0 : 0], own_off1 = p.out_off16[n_own > 1 ? own0 + 1 : 0];
+    unsigned int my_in_off[KH];
 #pragma unroll
-        for (int j = 0; j < KH; j++)
-            d[j] = (ok && j < ni) ? ld_vec(in_ptr[j] + off) : make_uint4(0, 0, 0, 0);
+    for (int j = 0; j < KH; j++) my_in_off[j] = p.in_off16[(j < ni) ? (j_base + j) : j_base];
+
+    struct Pos { const uint8_t *stripe; unsigned int v; bool ok; };
+    uint4 cur[KH];
+    auto locate_next = [&]() -> Pos {
+        Pos q;
+        const unsigned int v = ntt * RS_X2_THREADS + threadIdx.x;
+        q.ok = v <= last_vec;
+        q.v = q.ok ? v : last_vec;
+        q.stripe = p.base + sbase;
+        sbase += d_sbase;
+        ntt += step_tt;
+        if (ntt >= tps) { ntt -= tps; sbase += p.stripe_stride; }
+        return q;
     };
-    unsigned long long cur_off = 0;
-    bool cur_ok = false;
-    if (t < p.n_tiles) { cur_ok = locate_next(cur_off); load(cur, cur_off, cur_ok); }
+    auto load = [&](uint4 (&d)[KH], const Pos &q) {
+#pragma unroll
+        for (int j = 0; j < KH; j++) d[j] = ld_vec(q.stripe + static_cast<unsigned long long>(q.v + my_in_off[j]) * 16ull);
+    };
+    Pos cur_pos = {p.base, 0, false};
+    if (t < p.n_tiles) { cur_pos = locate_next(); load(cur, cur_pos); }
 
     uint4 keep0 = make_uint4(0, 0, 0, 0), keep1 = keep0;  // the rows this CTA owns, from the previous tile
-    unsigned long long keep_off = 0;
-    bool keep_ok = false, have_prev = false;
+    Pos keep_pos = {p.base, 0, false};
+    bool have_prev = false;
     unsigned int it = 0;
     // finish tile `it-1` (stage (it-1)&1, use (it-1)>>1): wait for the partner's rows, fold, store, free the slot
 #define RS_X2_FINISH_PREV()                                                                                          \
@@ -368,19 +371,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_X2_THREADS, 1) rs
             o1_.x ^= keep1.x; o1_.y ^= keep1.y; o1_.z ^= keep1.z; o1_.w ^= keep1.w;                                  \
             __syncwarp();                                                                                            \
             if (lane == 0) mbar_arrive_peer(peer_empty + ps_ * (NW * 8)); /* slot may be overwritten */              \
-            if (keep_ok) {                                                                                           \
-                *reinterpret_cast<uint4 *>(out_ptr0 + keep_off) = o0_;                                               \
-                if (n_own > 1) *reinterpret_cast<uint4 *>(out_ptr1 + keep_off) = o1_;                                \
+            if (keep_pos.ok) {                                                                                       \
+                uint8_t *ws_ = const_cast<uint8_t *>(keep_pos.stripe);                                               \
+                *reinterpret_cast<uint4 *>(ws_ + static_cast<unsigned long long>(keep_pos.v + own_off0) * 16ull) = o0_; \
+                if (n_own > 1) *reinterpret_cast<uint4 *>(ws_ + static_cast<unsigned long long>(keep_pos.v + own_off1) * 16ull) = o1_; \
             }                                                                                                        \
         }                                                                                                            \
     } while (0)
 
     for (; t < p.n_tiles; t += n_clusters, it++) {
         uint4 nxt[KH];
-        unsigned long long nxt_off = 0;
-        bool nxt_ok = false;
-        if (t + n_clusters < p.n_tiles) nxt_ok = locate_next(nxt_off);
-        load(nxt, nxt_off, nxt_ok);
+        Pos nxt_pos = cur_pos;
+        if (t + n_clusters < p.n_tiles) { nxt_pos = locate_next(); load(nxt, nxt_pos); }
 
         uint32_t acc[16];
 #pragma unroll
@@ -421,14 +423,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(RS_X2_THREADS, 1) rs
         if (have_prev) RS_X2_FINISH_PREV();  // the partner sent these a whole tile of work ago
         keep0 = own_a;
         keep1 = own_b;
-        keep_off = cur_off;
-        keep_ok = cur_ok;
+        keep_pos = cur_pos;
         have_prev = true;
 
 #pragma unroll
         for (int j = 0; j < KH; j++) cur[j] = nxt[j];
-        cur_ok = nxt_ok;
-        cur_off = nxt_off;
+        cur_pos = nxt_pos;
     }
     if (have_prev) RS_X2_FINISH_PREV();
 #undef RS_X2_FINISH_PREV
