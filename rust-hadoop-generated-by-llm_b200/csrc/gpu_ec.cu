@@ -164,6 +164,9 @@ struct Lease {
     ~Lease() { release(); }
     void release() {
         if (d && s) {
+            // every success path has already synchronised; on an early error return this drains copies that
+            // may still target caller memory before the slot (and its staging buffer) is handed on
+            if (cudaSetDevice(d->ordinal) == cudaSuccess) cudaStreamSynchronize(s->stream);
             std::lock_guard<std::mutex> lk(d->mu);
             s->busy = false;
             d->cv.notify_one();
@@ -859,6 +862,7 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
     if (len == 0) return GPU_EC_ERR_EMPTY_DATA;            // erasure.rs:11-13
     if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;    // ReedSolomon::new
     if (!data || !shards_out) return GPU_EC_ERR_INVALID_ARG;
+    for (int r = 0; r < m; r++) if (!shards_out[k + r]) return GPU_EC_ERR_INVALID_ARG;  // before any async copy is queued
     const int n = k + m;
     const size_t S = gpu_ec_shard_len(len, k);
     const size_t pitch = round_up(S, 256);
@@ -900,7 +904,6 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
             if (meta_out[i]) CK(cudaMemcpyAsync(meta_out[i], db + meta_off + 4 * n_meta * i, 4 * n_meta, cudaMemcpyDeviceToHost, st));
     }
     for (int r = 0; r < m; r++) {
-        if (!shards_out[k + r]) return GPU_EC_ERR_INVALID_ARG;
         CK(cudaMemcpyAsync(shards_out[k + r], db + static_cast<size_t>(k + r) * pitch, S, cudaMemcpyDeviceToHost, st));
     }
     // systematic data shards are the padded input verbatim (erasure.rs:17-19): host copy while the GPU works
@@ -926,6 +929,8 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
     if (shard_len == 0) return GPU_EC_ERR_EMPTY_SHARD;
     const int n = k + m;
     const size_t S = shard_len, pitch = round_up(S, 256);
+    for (int idx : plan.survivors) if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
+    for (int idx : plan.missing) if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
     Lease L;
     RET(lease_any(L));
     RET(slot_reserve(*L.s, static_cast<size_t>(n) * pitch));
@@ -933,14 +938,12 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
     uint8_t *db = L.s->dbuf;
     for (int j = 0; j < k; j++) {
         const int idx = plan.survivors[j];
-        if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
         CK(cudaMemcpyAsync(db + static_cast<size_t>(idx) * pitch, shards[idx], S, cudaMemcpyHostToDevice, st));
     }
     gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
     RET(launch_apply(*L.d, sv, plan.rows.data(), plan.survivors.data(), k, plan.missing.data(),
                      static_cast<int>(plan.missing.size()), st));
     for (int idx : plan.missing) {
-        if (!shards[idx]) return GPU_EC_ERR_INVALID_ARG;
         CK(cudaMemcpyAsync(shards[idx], db + static_cast<size_t>(idx) * pitch, S, cudaMemcpyDeviceToHost, st));
     }
     CK(cudaStreamSynchronize(st));
