@@ -391,6 +391,29 @@ def test_dev_crc_chunks_and_verify(L, orc):
     assert int(device.verify_chunks(t, 512, meta_u8).item()) == 10_000_000 // 512
 
 
+def test_dev_crc_chunks_many_buffers_with_fold(L, orc):
+    """Several pitched buffers, chunk sizes that need the fold (chunk > segment), ragged tails, both byte orders."""
+    import torch
+    n_buf, pitch = 5, 300_032
+    t = torch.empty(n_buf * pitch, dtype=torch.uint8, device="cuda")
+    from gpu_ec import device
+    device.fill_synthetic(t, 0xEC0000B7)
+    host = t.cpu().numpy().reshape(n_buf, pitch)
+    st = torch.cuda.current_stream().cuda_stream
+    for length, chunk in [(300_000, 4096), (299_999, 65_536), (8191, 2048), (262_144, 131_072), (300_000, 1536)]:
+        nch = (length + chunk - 1) // chunk
+        for be in (0, 1):
+            out = torch.zeros((n_buf, nch + 3), dtype=torch.int32, device="cuda")
+            _lib.check(L.gpu_ec_crc32_chunks_dev(t.data_ptr(), n_buf, pitch, length, chunk, 0, out.data_ptr(), nch + 3, be, st))
+            got = device.u32(out)
+            for b in range(n_buf):
+                want = orc.crc32_chunks(host[b, :length], chunk)
+                if be:
+                    want = want.byteswap()
+                assert np.array_equal(got[b, :nch], want), (length, chunk, be, b)
+                assert not got[b, nch:].any()  # nothing written past a buffer's own CRCs
+
+
 def test_dev_crc_unaligned_views(L, orc):
     """Device buffers that are not 16-byte aligned take the generic (still CUDA) kernel."""
     import torch
