@@ -3,7 +3,10 @@
 usage: python tools/exp_kernels.py crc|rs104|rs63 ..."""
 import ctypes as C
 import os
+import signal
 import sys
+
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)  # `| head -1` must not raise BrokenPipeError
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "rust-hadoop-generated-by-llm_b200"))
