@@ -67,8 +67,15 @@ struct CrcParams {
     int big_endian;                    // store byte-swapped (.meta layout, chunkserver.rs:196)
     const uint8_t *expect_be;          // verify mode: big-endian expected words (4-byte aligned) or null
     unsigned long long *first_bad;     // verify mode: atomicMin target
+    // fold32 mode (chunk == 32 segments): a warp's 32 lanes hold exactly the segments of ONE chunk, so the
+    // warp folds them itself (one carry-less multiply per lane + shuffles) and emits the chunk CRC:
+    // no per-segment scratch, no second kernel. f_c1[e] = x^(8*G*e), f_xrag = x^(8*rag).
+    int fold32;
+    uint32_t f_c1[32];
+    uint32_t f_xrag, f_poly;
 };
 
+__device__ __forceinline__ uint32_t multmodp_dev(uint32_t a, uint32_t b, uint32_t poly);
 __device__ __forceinline__ uint32_t bswap32(uint32_t v) { return __byte_perm(v, 0, 0x0123); }
 
 // `want` = the stored big-endian word of this segment, read as a little-endian u32; in verify mode
@@ -79,6 +86,8 @@ __device__ __forceinline__ void crc_emit(const CrcParams &p, unsigned long long 
     if (p.expect_be && want != bswap32(crc)) atomicMin(p.first_bad, seg);
 }
 
+// FOLD32: the in-warp fold of CrcParams::fold32, a compile-time variant so the plain path keeps its schedule
+template <bool FOLD32>
 __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __grid_constant__ CrcParams p) {
     extern __shared__ __align__(128) unsigned char crc_smem[];
     const int lane = threadIdx.x & 31;
@@ -98,11 +107,14 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
             asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(vq) : "memory");
         }
     }
-    __syncthreads();
-
     // staging box of this warp: below block A while there is room, the rest above block B
     const uint32_t s0a = (s0 + 127u) & ~127u;
     const int n1 = static_cast<int>((CRC_BLK_A - s0a) / CRC_BOX_BYTES);
+    // fold32 constants behind the last box (a lane-indexed read of the parameter bank would replay 32x)
+    const uint32_t cc_s = CRC_REGION2 + (CRC_WARPS > n1 ? (CRC_WARPS - n1) : 0) * CRC_BOX_BYTES;
+    if (FOLD32 && threadIdx.x < 32) asm volatile("st.shared.u32 [%0], %1;" ::"r"(cc_s + threadIdx.x * 4), "r"(p.f_c1[threadIdx.x]) : "memory");
+    __syncthreads();
+
     const uint32_t box_s = (warp < n1) ? (s0a + warp * CRC_BOX_BYTES) : (CRC_REGION2 + (warp - n1) * CRC_BOX_BYTES);
     const uint4 *box = reinterpret_cast<const uint4 *>(crc_smem + (box_s - s0));
     const uint32_t lb_a = CRC_BLK_A | static_cast<uint32_t>(lane * 4), lb_b = CRC_BLK_B | static_cast<uint32_t>(lane * 4);
@@ -207,8 +219,12 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
             col++;
         }
         if (tile < n_tiles) issue_loads(col);
-        if (cur_col == 0 && p.expect_be && seg < p.segs_per_buf)
-            want = __ldg(reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * seg));
+        if constexpr (FOLD32) {  // expected word of the CHUNK, kept by lane 0
+            if (cur_col == 0 && p.expect_be && lane == 0) want = __ldg(reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * (seg / 32ull)));
+        } else {
+            if (cur_col == 0 && p.expect_be && seg < p.segs_per_buf)
+                want = __ldg(reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * seg));
+        }
         if (cur_col < cols_of(seg)) {
 #pragma unroll
             for (int q = 0; q < 8; q++) {
@@ -219,16 +235,39 @@ __global__ void __launch_bounds__(CRC_THREADS, 1) crc_segments_kernel(const __gr
             }
         }
         if (last_col) {
-            if (seg < p.nfull) {
-                crc_emit(p, buf, seg, ~c, want);
-            } else if (seg == p.nfull && p.rag) {
-                // the ragged segment: its last (rag % 128) bytes straight from global
+            auto ragged_tail = [&]() {  // the ragged segment's last (rag % 128) bytes straight from global
                 const uint8_t *src = p.base + buf * p.buf_stride + p.nfull * p.G + (static_cast<unsigned long long>(ncol_rag) << 7);
                 const unsigned int left = p.rag & 127u;
                 unsigned int i = 0;
                 for (; i + 4 <= left; i += 4) c = step_word(c, *reinterpret_cast<const uint32_t *>(src + i));
                 for (; i < left; i++) c = (c >> 8) ^ CRC_LUT(lb_b, 1, c ^ src[i], 0);
-                crc_emit(p, buf, seg, ~c, want);
+            };
+            if constexpr (!FOLD32) {
+                if (seg < p.nfull) {
+                    crc_emit(p, buf, seg, ~c, want);
+                } else if (seg == p.nfull && p.rag) {
+                    ragged_tail();
+                    crc_emit(p, buf, seg, ~c, want);
+                }
+            } else {
+                // this warp's lanes are the segments of one chunk: weight lane l by x^(8*G*(nft-1-l)), XOR-reduce,
+                // then append the ragged segment (if the buffer ends in this chunk): fold * x^(8*rag) ^ p_rag
+                if (seg == p.nfull && p.rag) ragged_tail();
+                const unsigned long long seg0 = seg - lane;
+                const unsigned int nft = (p.nfull > seg0) ? static_cast<unsigned int>(p.nfull - seg0 < 32 ? p.nfull - seg0 : 32) : 0u;
+                const uint32_t mine = ~c;
+                uint32_t f = 0;
+                if (static_cast<unsigned int>(lane) < nft) {
+                    uint32_t w_;
+                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w_) : "r"(cc_s + (nft - 1u - lane) * 4u));
+                    f = multmodp_dev(mine, w_, p.f_poly);
+                }
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) f ^= __shfl_xor_sync(0xffffffffu, f, sft);
+                const bool rag_here = p.rag && nft < 32 && (seg0 + nft == p.nfull);
+                const uint32_t p_rag = __shfl_sync(0xffffffffu, mine, static_cast<int>(nft & 31u));
+                if (rag_here) f = multmodp_dev(f, p.f_xrag, p.f_poly) ^ p_rag;
+                if (lane == 0 && (nft || rag_here)) crc_emit(p, buf, seg0 / 32ull, f, want);
             }
             c = 0xFFFFFFFFu;
         }

@@ -101,7 +101,8 @@ static int dev_prepare(Dev &d) {
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(4)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(5)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(6)));
-    CK(cudaFuncSetAttribute(crc_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(crc_segments_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(crc_segments_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
     for (auto &s : d.slots) CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     // keep stream-ordered scratch cached instead of returning it to the OS after every call
     cudaMemPool_t pool;
@@ -472,6 +473,7 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
                          !(j.expect_be && (reinterpret_cast<uintptr_t>(j.expect_be) & 3));
     const unsigned long long lanes_wave = static_cast<unsigned long long>(d.sm_count) * CRC_THREADS;
     size_t G = 0;
+    bool fold32 = false;
     if (aligned) {
         const unsigned long long total = static_cast<unsigned long long>(j.n_buf) * j.len;
         if (whole) {
@@ -479,6 +481,9 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
         } else if (j.chunk % 128 == 0) {
             if (j.chunk <= 1024) {
                 G = j.chunk;  // one lane per chunk, CRC written directly
+            } else if (j.chunk % 4096 == 0 && j.chunk / 32 <= 4096) {
+                G = j.chunk / 32;  // 16..128 KiB chunks: a warp's 32 lanes are one chunk, folded in the kernel
+                fold32 = true;
             } else {
                 for (size_t g : {size_t(4096), size_t(2048), size_t(1024), size_t(512)})
                     if (j.chunk % g == 0 && total / g >= 4 * lanes_wave) { G = g; break; }
@@ -512,7 +517,16 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     p.segs_per_buf = p.nfull + (p.rag ? 1 : 0);
     p.tiles_per_buf = div_up(p.segs_per_buf, 32);
     p.poly = j.poly;
-    const bool direct = !whole && G == j.chunk;
+    const bool direct = !whole && (G == j.chunk || fold32);
+    if (fold32) {
+        const uint32_t P = kPolyReflected[j.poly];
+        p.fold32 = 1;
+        p.f_poly = P;
+        p.f_xrag = x8n_modp(p.rag, P);
+        const uint32_t xg = x8n_modp(G, P);
+        p.f_c1[0] = 0x80000000u;
+        for (int e = 1; e < 32; e++) p.f_c1[e] = multmodp(p.f_c1[e - 1], xg, P);
+    }
     uint32_t *scratch = nullptr;
     const size_t group = whole ? static_cast<size_t>(p.segs_per_buf) : j.chunk / G;
     const size_t n_part = static_cast<size_t>(j.n_buf) * p.segs_per_buf;
@@ -526,7 +540,8 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     }
     const unsigned long long warps = j.n_buf * p.tiles_per_buf;
     const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(d.sm_count))));
-    crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
+    if (fold32) crc_segments_kernel<true><<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
+    else crc_segments_kernel<false><<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     g_launches++;
     CK(cudaGetLastError());
     if (!direct) {
@@ -1311,7 +1326,7 @@ int noalloc_setup(int ordinal, NoAllocDev **out) {
         static std::once_flag once;
         std::call_once(once, [] { for (int p = 0; p < 2; p++) crc_tables(kPolyReflected[p], tabs[p]); });
         CK(cudaMemcpyToSymbol(g_crc_tab, tabs, sizeof tabs));  // same bytes dev_prepare uploads; no allocation
-        CK(cudaFuncSetAttribute(crc_segments_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+        CK(cudaFuncSetAttribute(crc_segments_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
         nd.scratch = static_cast<uint32_t *>(addr);
         nd.shim.ordinal = ordinal;
         nd.shim.sm_count = sms;
@@ -1382,7 +1397,7 @@ int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_strid
     p.out_stride = p.segs_per_buf;
     const unsigned long long warps = n_buf * p.tiles_per_buf;
     const int grid = static_cast<int>(std::max<unsigned long long>(1, std::min<unsigned long long>(div_up(warps, CRC_WARPS), static_cast<unsigned long long>(sms))));
-    crc_segments_kernel<<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
+    crc_segments_kernel<false><<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     g_launches++;
     CK(cudaGetLastError());
     return launch_combine(nd->shim, nd->scratch, n_buf, p.segs_per_buf, G, len, p.segs_per_buf, j, st,
