@@ -141,7 +141,8 @@ int gpu_ec_verify_chunks_batch(size_t n_blocks, const uint8_t *const *data, cons
 /* n_stripes stripes of k+m shard slots in device memory:
  * slot s of stripe i starts at base + i*stripe_stride + s*shard_stride and holds shard_len bytes.
  * base and both strides must be multiples of 16 and shard_stride >= round_up(shard_len, 16):
- * kernels move whole 16-byte vectors and may overwrite the pad bytes of OUTPUT slots. */
+ * kernels move whole 16-byte vectors and may overwrite the pad bytes of OUTPUT slots. Every slot a
+ * call touches must lie within 64 GiB of its stripe's start (slot offsets are 32-bit vector indices). */
 typedef struct gpu_ec_stripes {
     uint8_t *base;
     size_t shard_stride;

@@ -221,7 +221,6 @@ static int check_stripes(const gpu_ec_stripes *s) {
     if (!s || !s->base) return GPU_EC_ERR_INVALID_ARG;
     if ((reinterpret_cast<uintptr_t>(s->base) & 15) || (s->shard_stride & 15) || (s->stripe_stride & 15)) return GPU_EC_ERR_UNALIGNED;
     if (s->shard_stride < round_up(s->shard_len, 16)) return GPU_EC_ERR_INVALID_ARG;
-    if (s->shard_stride / 16 * 256 >= (1ull << 32)) return GPU_EC_ERR_INVALID_ARG;  // slot offsets are 32-bit vector indices
     return GPU_EC_OK;
 }
 
@@ -306,6 +305,15 @@ static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows,
     return GPU_EC_OK;
 }
 
+// slot offsets travel to the kernels as 32-bit indices of 16-byte vectors: every used slot must start and end
+// below 64 GiB from the stripe's base (a 7 GiB shard at RS(6,3); the reference caps shards at 100 MiB)
+static bool slots_addressable(const gpu_ec_stripes &s, const int *in_idx, int n_in, const int *out_idx, int n_out) {
+    unsigned long long hi = 0;
+    for (int j = 0; j < n_in; j++) hi = std::max<unsigned long long>(hi, static_cast<unsigned long long>(in_idx[j]));
+    for (int r = 0; r < n_out; r++) hi = std::max<unsigned long long>(hi, static_cast<unsigned long long>(out_idx[r]));
+    return (hi + 1) * (s.shard_stride / 16) < (1ull << 32);
+}
+
 // out slot out_idx[r] = XOR_j rows[r*n_in+j] * in slot in_idx[j].
 // n_in <= 7 and n_out <= 4: ONE pass of the byte-LUT kernel over everything.
 // Otherwise several passes (output rows in groups of 4; inputs in balanced groups of <= 7 for the
@@ -317,6 +325,12 @@ static int launch_apply(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, co
                         const int *out_idx, int n_out, cudaStream_t st) {
     if (n_in <= 0 || n_out <= 0) return GPU_EC_ERR_INVALID_ARG;
     if (s.n_stripes == 0 || s.shard_len == 0) return GPU_EC_OK;
+    for (int j = 0; j < n_in; j++) if (in_idx[j] < 0) return GPU_EC_ERR_INVALID_ARG;
+    for (int r = 0; r < n_out; r++) if (out_idx[r] < 0) return GPU_EC_ERR_INVALID_ARG;
+    if (!slots_addressable(s, in_idx, n_in, out_idx, n_out)) {
+        t_last_error = "stripe too large: a used shard slot lies 64 GiB or more past the stripe base";
+        return GPU_EC_ERR_INVALID_ARG;
+    }
     if (n_in <= RS_LUT8_MAX_IN && n_out <= RS_MAX_OUT)
         return launch_apply_pass(d, s, rows, n_in, in_idx, n_in, out_idx, n_out, false, true, st);
     static const bool no_cluster = getenv("GPU_EC_NO_CLUSTER") != nullptr;  // kernel experiments only
