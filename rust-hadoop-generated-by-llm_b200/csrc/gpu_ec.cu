@@ -170,7 +170,7 @@ struct Lease {
             if (cudaSetDevice(d->ordinal) == cudaSuccess) cudaStreamSynchronize(s->stream);
             std::lock_guard<std::mutex> lk(d->mu);
             s->busy = false;
-            d->cv.notify_one();
+            d->cv.notify_all();
         }
         d = nullptr; s = nullptr;
     }
@@ -186,6 +186,26 @@ static int lease_on(Dev &d, Lease &l) {
         });
         s->busy = true;
         l.d = &d; l.s = s;
+    }
+    CK(cudaSetDevice(d.ordinal));
+    return GPU_EC_OK;
+}
+
+// n slots of one device, all or nothing: two batch callers that each grabbed some and waited for the rest
+// would deadlock, so the wait is for n free slots at once
+static int lease_n_on(Dev &d, int n, Lease *out) {
+    {
+        std::unique_lock<std::mutex> lk(d.mu);
+        d.cv.wait(lk, [&] {
+            int free_slots = 0;
+            for (auto &x : d.slots) free_slots += x.busy ? 0 : 1;
+            return free_slots >= n;
+        });
+        int got = 0;
+        for (auto &x : d.slots) {
+            if (got == n) break;
+            if (!x.busy) { x.busy = true; out[got].d = &d; out[got].s = &x; got++; }
+        }
     }
     CK(cudaSetDevice(d.ordinal));
     return GPU_EC_OK;
@@ -1129,7 +1149,7 @@ struct BatchLanes {
             Dev *d;
             RET(get_dev(act[a], &d));
             devs.push_back(d);
-            for (int s = 0; s < slots_per_dev; s++) RET(lease_on(*d, leases[a * slots_per_dev + s]));
+            RET(lease_n_on(*d, slots_per_dev, &leases[a * slots_per_dev]));
         }
         return GPU_EC_OK;
     }

@@ -483,6 +483,32 @@ def test_host_batches(L, orc):
     assert np.array_equal(broken, shards)
 
 
+def test_concurrent_batch_callers(L, orc):
+    """Several threads inside the _batch entry points at once (each wants 3 of a device's 4 slots): the
+    slots are leased all-or-nothing, so the callers queue instead of deadlocking."""
+    k, m, stripe_len, n = 6, 3, 300_000, 6
+    S = erasure.shard_len(stripe_len, k)
+    errs = []
+
+    def work(tid):
+        try:
+            data = orc.fill_synthetic(stripe_len * n, 1000 + tid)
+            parity = np.empty((n, m, S), np.uint8)
+            for _ in range(3):
+                _lib.check(L.gpu_ec_encode_batch(data.ctypes.data, stripe_len, n, k, m, parity.ctypes.data, None, None))
+            want = orc.encode(data[:stripe_len], k, m)
+            assert np.array_equal(parity[0], want[k:])
+            assert checksum.crc32(data[:70_000]) == zlib.crc32(data[:70_000].tobytes())
+        except Exception as e:  # noqa: BLE001
+            errs.append((tid, repr(e)))
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(6)]
+    [t.start() for t in th]
+    [t.join(timeout=120) for t in th]
+    assert not any(t.is_alive() for t in th), "batch callers deadlocked"
+    assert not errs, errs
+
+
 def test_pinned_alloc_roundtrip(L, orc):
     p = C.c_void_p()
     n = 1 << 20
