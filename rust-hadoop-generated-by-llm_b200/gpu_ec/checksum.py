@@ -176,6 +176,28 @@ class BlockStore:
         self.write_block(block_id, shard)
         return int(shard.size)
 
+    def convert_block_to_ec(self, block_id: str, data_shards: int, parity_shards: int) -> dict:
+        """The byte work of the chunkserver-side "EC encode and distribute" command the reference leaves
+        as a TODO (metaserver/src/master.rs:2108-2113): verify the stored replicated block, encode it,
+        and store every shard as `<block_id>_shard<i>` with its .meta — shards, their .meta arrays, the
+        per-shard CRCs (WriteBlock's expected_checksum) and CRC(original) all come from ONE H2D of the block.
+        -> {"shard_ids", "shard_checksums", "full_checksum", "original_size"}."""
+        from . import erasure
+        with open(os.path.join(self.storage_dir, block_id), "rb") as f:
+            data = np.frombuffer(f.read(), dtype=np.uint8)
+        self.verify_block(block_id, data)
+        shards, crcs, full, metas = erasure.encode_with_checksums(data, data_shards, parity_shards, with_meta=True)
+        ids = []
+        for i, (sh, mt) in enumerate(zip(shards, metas)):
+            sid = f"{block_id}_shard{i}"
+            with open(os.path.join(self.storage_dir, sid), "wb") as f:
+                f.write(sh.tobytes())
+            with open(os.path.join(self.storage_dir, sid + ".meta"), "wb") as f:
+                f.write(mt.tobytes())
+            ids.append(sid)
+        return {"shard_ids": ids, "shard_checksums": [int(c) for c in crcs], "full_checksum": int(full),
+                "original_size": int(data.size)}
+
     def write_block(self, block_id: str, data) -> None:
         """write_block_async (chunkserver.rs:192-209): data file + big-endian .meta sidecar."""
         d = _as_u8(data)

@@ -661,3 +661,24 @@ def test_reconstruct_only_wanted_slots(L, orc):
     opt[2] = None
     with pytest.raises(erasure.ErasureError, match="invalid argument"):
         erasure.reconstruct_only(opt, 6, 3, [3])  # slot 3 is present
+
+
+def test_convert_stored_block_to_ec(L, orc, tmp_path):
+    """SURVEY §8(f) item 3 (master.rs:2108-2113 TODO): replicated block -> RS(6,3) shards on the chunkserver."""
+    store = checksum.BlockStore(str(tmp_path))
+    data = rnd(3_000_001, 21)
+    store.write_block("cold", data)
+    info = store.convert_block_to_ec("cold", 6, 3)
+    want = orc.encode(data, 6, 3)
+    assert info["original_size"] == data.size and info["full_checksum"] == zlib.crc32(data.tobytes())
+    assert info["shard_checksums"] == [zlib.crc32(s.tobytes()) for s in want]
+    for i, sid in enumerate(info["shard_ids"]):
+        raw = np.frombuffer((tmp_path / sid).read_bytes(), dtype=np.uint8)
+        assert np.array_equal(raw, want[i])
+        store.verify_block(sid, raw)  # the .meta written from the encode call verifies like any block
+    assert store.scrub() == (10, [])
+    # degraded read from the stored shards (client/src/mod.rs:1110-1165)
+    from gpu_ec import client
+    opt = [None if i in (0, 4, 8) else np.frombuffer((tmp_path / sid).read_bytes(), dtype=np.uint8)
+           for i, sid in enumerate(info["shard_ids"])]
+    assert np.array_equal(client.read_ec_block("cold", opt, 6, 3, info["original_size"]), data)
