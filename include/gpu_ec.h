@@ -161,7 +161,10 @@ int gpu_ec_apply_matrix_dev(const gpu_ec_stripes *s, const uint8_t *rows, const 
                             const int *out_idx, int n_out, void *stream);
 /* n_buf buffers of `len` bytes at base + b*buf_stride; per buffer ceil(len/chunk) CRCs written to
  * out + b*out_stride (in words). big_endian != 0 stores each word byte-swapped (.meta layout).
- * Requires base, buf_stride multiples of 16. Uses stream-ordered scratch when chunk > 512. */
+ * base and buf_stride should be multiples of 16 and chunk a multiple of 128 (otherwise a slower generic
+ * kernel runs). Chunks up to 1 KiB and chunks of 16-128 KiB (multiples of 4 KiB) are hashed and, where
+ * needed, folded inside one kernel; other sizes keep per-segment CRCs in stream-ordered scratch
+ * (cudaMallocAsync on `stream`) and fold them with a second kernel. */
 int gpu_ec_crc32_chunks_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len,
                             size_t chunk, int poly, uint32_t *out, size_t out_stride,
                             int big_endian, void *stream);
