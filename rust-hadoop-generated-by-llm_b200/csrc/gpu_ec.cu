@@ -19,6 +19,7 @@
 #include "crc_kernels.cuh"
 #include "host_math.hpp"
 #include "rs_kernels.cuh"
+#include "sfold_kernels.cuh"
 
 namespace gpu_ec {
 
@@ -406,6 +407,7 @@ struct CrcJob {
     int big_endian = 0;
     const uint8_t *expect_be = nullptr;
     unsigned long long *first_bad = nullptr;
+    bool no_sfold = false;     // keep whole-buffer mode on the table kernel (the sparse-fold finisher's own dump rows)
 };
 
 // words of second-level scratch launch_combine needs for outputs of up to `maxcnt` full elements
@@ -493,6 +495,143 @@ static size_t pick_whole_segment(const Dev &d, size_t n_buf, size_t len) {
     return G_CAP;
 }
 
+// ---------------------------------------------------------------------------------------------
+// sparse-fold whole-buffer CRC (sfold_kernels.cuh)
+
+struct SfoldPlan {
+    SfoldGeom g;
+    unsigned int tw = 0, n_class = 0;     // columns per CTA, CTAs per row
+    unsigned long long nvec = 0;
+    size_t n_streams = 0;                 // n_buf * n_seg
+    size_t dump_bytes = 0, qlog_bytes = 0;  // scratch, whole job
+};
+
+// knob for experiments and for the tests that pin each path: GPU_EC_SFOLD=0 keeps whole-buffer CRCs on
+// the table kernel, =1 (default) lets large aligned IEEE buffers take the sparse-fold kernels
+static bool sfold_enabled() {
+    const char *e = getenv("GPU_EC_SFOLD");
+    return !e || e[0] != '0';
+}
+
+// geometry for n_buf buffers of `len` bytes walked by CTAs of `tw_fixed` threads (0 = pick 256..512).
+// want_ctas = CTAs the launch can keep busy at once. false = not worth it (too short for any stride).
+static bool sfold_plan(size_t n_buf, size_t len, unsigned int tw_fixed, size_t want_ctas, bool allow_segments, SfoldPlan &pl) {
+    const unsigned long long nvec = div_up(len, 16);
+    double best = -1.0;
+    for (int e = 0; e < kSfoldIeeeCount; e++) {
+        const SfoldStride &sd = kSfoldIeee[e];
+        const unsigned long long rows = div_up(nvec, sd.dv);
+        if (rows < 6) break;
+        unsigned int tw = tw_fixed;
+        if (!tw) {
+            double bf = 0;
+            for (unsigned int c = 256; c <= 512; c += 32) {
+                const double f = static_cast<double>(sd.dv) / (static_cast<double>(c) * div_up(sd.dv, c));
+                if (f > bf + 1e-9) { bf = f; tw = c; }
+            }
+        }
+        const unsigned int n_class = static_cast<unsigned int>(div_up(sd.dv, tw));
+        const double fill = static_cast<double>(sd.dv) / (static_cast<double>(tw) * n_class);
+        unsigned long long n_seg = 1;
+        if (allow_segments) {
+            const unsigned long long max_seg = std::max<unsigned long long>(1, rows / 24);
+            n_seg = std::min<unsigned long long>(max_seg, std::max<unsigned long long>(1, div_up(4 * want_ctas, n_buf * n_class)));
+        }
+        const unsigned long long rseg = div_up(rows, n_seg);
+        n_seg = div_up(rows, rseg);
+        const double jobs = static_cast<double>(n_buf) * n_seg * n_class;
+        const double busy = std::min(1.0, jobs / static_cast<double>(want_ctas));
+        const double score = fill * busy / (1.0 + 2.0 / static_cast<double>(rseg) + 0.03);
+        if (score > best) {
+            best = score;
+            pl.g.dv = sd.dv;
+            pl.g.ng = static_cast<unsigned int>(div_up(sd.dv, 32));
+            pl.g.rseg = static_cast<unsigned int>(rseg);
+            pl.g.n_seg = static_cast<unsigned int>(n_seg);
+            const unsigned long long lead = n_seg * rseg * sd.dv - nvec;  // virtual zero vectors in front of the buffer
+            pl.g.skip_rows = static_cast<unsigned int>(lead / sd.dv);
+            pl.g.lead = static_cast<unsigned int>(lead % sd.dv);
+            for (int t = 0; t < 4; t++) pl.g.sh[t] = sd.k[t] & 31u;
+            pl.tw = tw;
+            pl.n_class = n_class;
+        }
+    }
+    if (best < 0) return false;
+    pl.nvec = nvec;
+    pl.n_streams = n_buf * pl.g.n_seg;
+    pl.dump_bytes = pl.n_streams * static_cast<size_t>(pl.g.dv) * 16;
+    pl.qlog_bytes = pl.n_streams * static_cast<size_t>(pl.g.rseg) * pl.g.ng * 8;
+    return true;
+}
+
+static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st);
+
+// finisher for n_buf buffers whose dump rows and lost-bit logs are in place: CRC the dump rows with the table
+// kernel, then fold everything into out[b * out_stride]
+static int launch_sfold_finish(Dev &d, const SfoldPlan &pl, size_t n_buf, size_t len, const uint4 *dump, const uint2 *qlog,
+                               uint32_t *dump_crc, uint32_t *out, size_t out_stride, cudaStream_t st) {
+    const uint32_t P = kPolyReflected[0];
+    CrcJob j;
+    j.base = reinterpret_cast<const uint8_t *>(dump); j.n_buf = pl.n_streams; j.buf_stride = static_cast<size_t>(pl.g.dv) * 16;
+    j.len = j.buf_stride; j.chunk = 0; j.poly = 0; j.out = dump_crc; j.out_stride = 1; j.no_sfold = true;
+    RET(launch_crc(d, j, st));
+    SfoldFinishParams f;
+    memset(&f, 0, sizeof f);
+    f.qlog = qlog; f.dump_crc = dump_crc; f.out = out; f.out_stride = out_stride; f.n_buf = n_buf;
+    f.g = pl.g;
+    f.per_thread = static_cast<unsigned int>(div_up(pl.g.ng, 256));
+    f.poly_bits = P;
+    f.xD = x8n_modp(16ull * pl.g.dv, P);
+    f.x32 = x8n_modp(4, P);
+    f.y = x8n_modp(512, P);
+    uint32_t zp = 0x80000000u;
+    for (unsigned int i = 0; i < f.per_thread; i++) zp = multmodp(zp, f.y, P);
+    for (int L = 0; L < 8; L++) { f.z[L] = zp; zp = multmodp(zp, zp, P); }
+    const unsigned int tail_cols = pl.g.dv - 32u * (pl.g.ng - 1);
+    f.x_tail = x8n_modp(16ull * tail_cols + 4, P);
+    f.cz_dump = crc_of_zeros(16ull * pl.g.dv, P);
+    f.x_seg = x8n_modp(16ull * pl.g.dv * pl.g.rseg, P);
+    f.x_inv_pad = xinv8n_modp(pl.nvec * 16 - len, P);
+    f.cz_len = crc_of_zeros(len, P);
+    const int grid = static_cast<int>(std::min<size_t>(n_buf, static_cast<size_t>(d.sm_count) * 4));
+    crc_sfold_finish_kernel<<<grid, 256, 0, st>>>(f);
+    g_launches++;
+    CK(cudaGetLastError());
+    return GPU_EC_OK;
+}
+
+static void sfold_tail_mask(size_t len, uint32_t (&mask)[4]) {
+    const size_t keep = len % 16 ? len % 16 : 16;
+    for (int w = 0; w < 4; w++) {
+        uint32_t m = 0;
+        for (int b = 0; b < 4; b++) if (static_cast<size_t>(4 * w + b) < keep) m |= 0xFFu << (8 * b);
+        mask[w] = m;
+    }
+}
+
+// whole-buffer CRC-32 (IEEE) of n_buf 16-byte-aligned buffers, out[b * out_stride]
+static int launch_sfold_crc(Dev &d, const SfoldPlan &pl, const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len,
+                            uint32_t *out, size_t out_stride, cudaStream_t st) {
+    uint8_t *scratch = nullptr;
+    const size_t dump_off = 0, qlog_off = round_up(pl.dump_bytes, 256), crc_off = qlog_off + round_up(pl.qlog_bytes, 256);
+    CK(cudaMallocAsync(&scratch, crc_off + 4 * pl.n_streams, st));
+    SfoldParams p;
+    memset(&p, 0, sizeof p);
+    p.base = base; p.buf_stride = buf_stride; p.n_buf = n_buf; p.nvec = pl.nvec; p.g = pl.g; p.n_class = pl.n_class;
+    sfold_tail_mask(len, p.tail_mask);
+    p.dump = reinterpret_cast<uint4 *>(scratch + dump_off);
+    p.qlog = reinterpret_cast<uint2 *>(scratch + qlog_off);
+    const unsigned long long jobs = static_cast<unsigned long long>(n_buf) * pl.g.n_seg * pl.n_class;
+    const int grid = static_cast<int>(std::min<unsigned long long>(jobs, static_cast<unsigned long long>(d.sm_count) * 2));
+    crc_sfold_kernel<<<grid, pl.tw, 0, st>>>(p);
+    g_launches++;
+    int rc = (cudaGetLastError() == cudaSuccess) ? GPU_EC_OK : GPU_EC_ERR_CUDA;
+    if (rc == GPU_EC_OK)
+        rc = launch_sfold_finish(d, pl, n_buf, len, p.dump, p.qlog, reinterpret_cast<uint32_t *>(scratch + crc_off), out, out_stride, st);
+    cudaFreeAsync(scratch, st);
+    return rc;
+}
+
 static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     if (j.n_buf == 0) return GPU_EC_OK;
     const bool whole = (j.chunk == 0);
@@ -505,6 +644,12 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     }
     const bool aligned = !(reinterpret_cast<uintptr_t>(j.base) & 15) && !(j.buf_stride & 15) &&
                          !(j.expect_be && (reinterpret_cast<uintptr_t>(j.expect_be) & 3));
+    if (whole && aligned && j.poly == 0 && !j.expect_be && j.out && !j.no_sfold && j.len >= (256u << 10) &&
+        j.n_buf * j.len >= (8u << 20) && sfold_enabled()) {
+        SfoldPlan pl;
+        if (sfold_plan(j.n_buf, j.len, 0, static_cast<size_t>(d.sm_count) * 2, true, pl))
+            return launch_sfold_crc(d, pl, j.base, j.n_buf, j.buf_stride, j.len, j.out, j.out_stride, st);
+    }
     const unsigned long long lanes_wave = static_cast<unsigned long long>(d.sm_count) * CRC_THREADS;
     size_t G = 0;
     bool fold32 = false;
@@ -597,14 +742,8 @@ static void full_crc_constants(FullCrcParams &f, size_t S, size_t original_len, 
     f.has_part = rem ? 1 : 0;
     f.xS = x8n_modp(S, P);
     f.xLp = x8n_modp(rem, P);
-    // x^-1: undo one "multiply by x" step; then raise to 8*pad
-    const uint32_t xinv = ((0x80000000u ^ P) << 1) | 1u;
-    uint32_t r = 0x80000000u, sq = xinv;
-    for (uint64_t e = 8ull * pad; e; e >>= 1) { if (e & 1) r = multmodp(sq, r, P); sq = multmodp(sq, sq, P); }
-    f.x_inv_pad = r;
-    uint32_t c = 0xFFFFFFFFu;  // CRC of `pad` zero bytes
-    for (size_t i = 0; i < pad; i++) for (int b = 0; b < 8; b++) c = (c >> 1) ^ ((c & 1) ? P : 0);
-    f.crc_zeros_pad = pad ? ~c : 0u;
+    f.x_inv_pad = xinv8n_modp(pad, P);
+    f.crc_zeros_pad = crc_of_zeros(pad, P);  // O(log pad): original_len may be far below k*S on the _dev entry
     f.poly_bits = P;
 }
 static uint32_t full_crc_host(const uint32_t *shard_crc, size_t S, size_t original_len, int poly) {

@@ -167,6 +167,19 @@ inline uint32_t x8n_modp(uint64_t n, uint32_t poly) {
     }
     return p;
 }
+// x^(-8 n) mod P: x^-1 = (P + 1)/x exists because P has a constant term
+inline uint32_t xinv8n_modp(uint64_t n, uint32_t poly) {
+    uint32_t r = 0x80000000u, sq = ((0x80000000u ^ poly) << 1) | 1u;
+    for (uint64_t e = 8ull * n; e; e >>= 1) {
+        if (e & 1) r = multmodp(sq, r, poly);
+        sq = multmodp(sq, sq, poly);
+    }
+    return r;
+}
+// CRC-32 (init and xorout 0xFFFFFFFF) of n zero bytes in O(log n): the register is just multiplied by x^8 per byte
+inline uint32_t crc_of_zeros(uint64_t n, uint32_t poly) {
+    return n ? (multmodp(0xFFFFFFFFu, x8n_modp(n, poly), poly) ^ 0xFFFFFFFFu) : 0u;
+}
 // slice-by-4 tables T[t][b] uploaded once per device
 inline void crc_tables(uint32_t poly, uint32_t (*T)[256]) {
     for (uint32_t i = 0; i < 256; i++) {

@@ -618,9 +618,31 @@ def test_two_devices_in_one_process(L, orc):
             want = orc.encode(data[i * stripe_len:(i + 1) * stripe_len], k, m)
             assert np.array_equal(parity[i], want[k:]), i
             assert crcs[i].tolist() == [zlib.crc32(s.tobytes()) for s in want]
-        for i in range(4):  # single calls alternate between the devices too
+        # reconstruct batch across both devices (chunkserver.rs:620-623 per stripe)
+        shards = np.empty((n, k + m, S), np.uint8)
+        for i in range(n):
+            shards[i] = orc.encode(data[i * stripe_len:(i + 1) * stripe_len], k, m)
+        broken = shards.copy()
+        broken[:, [1, 4, 7]] = 0
+        present = np.array([1, 0, 1, 1, 0, 1, 1, 0, 1], np.uint8)
+        _lib.check(L.gpu_ec_reconstruct_batch(broken.ctypes.data, present.ctypes.data, S, n, k, m))
+        assert np.array_equal(broken, shards)
+        # batched verify across both devices (chunkserver.rs:275-289 per block): verdicts per block
+        blocks = [rnd(sz, 40 + j) for j, sz in enumerate((61, 65_536, 1_000_003, 3 << 20, 600, 2_000_000, 512))]
+        metas = [orc.meta_encode_be(orc.crc32_chunks(b)) for b in blocks]
+        bad = blocks[2].copy()
+        bad[777_777] ^= 1
+        blocks[2] = bad
+        got = checksum.verify_blocks(blocks, metas)
+        assert got == [None, None, f"Checksum mismatch at chunk {777_777 // 512}", None, None, None, None]
+        for i in range(6):  # single calls round-robin over the devices (lease_any) too
             d = rnd(70_001 + i, i)
             assert checksum.crc32(d) == zlib.crc32(d.tobytes())
+            sh = erasure.encode(d, 4, 2)
+            want = orc.encode(d, 4, 2)
+            assert all(np.array_equal(a, b) for a, b in zip(sh, want))
+            opt = [None if j in (0, 5) else want[j].copy() for j in range(6)]
+            assert np.array_equal(erasure.decode(opt, 4, 2, d.size), d)
     finally:
         one = (C.c_int * 1)(0)
         _lib.check(L.gpu_ec_set_devices(one, 1))

@@ -51,6 +51,27 @@ def crc():
     print(f"crc whole 140x6.7MB: {ms*1e3:.1f} us  {140*S/ms/1e6:.0f} GB/s")
 
 
+def sfold():
+    """whole-buffer CRC: sparse-fold kernels vs the table kernel, same buffers"""
+    st = torch.cuda.current_stream().cuda_stream
+    for n_buf, S in ((140, 6710887), (1400, 6710887), (14, 6710887), (1, 1 << 30), (64, 11184811), (1, 64 << 20)):
+        pitch = (S + 255) // 256 * 256
+        t = torch.empty(n_buf * pitch, dtype=torch.uint8, device="cuda")
+        device.fill_synthetic(t, 2)
+        o = torch.empty(n_buf, dtype=torch.int32, device="cuda")
+        res = {}
+        for mode in ("1", "0"):
+            os.environ["GPU_EC_SFOLD"] = mode
+            l0 = L.gpu_ec_kernel_launch_count()
+            ms = timed(lambda: check(L.gpu_ec_crc32_dev(t.data_ptr(), n_buf, pitch, S, 0, o.data_ptr(), st)), 10)
+            res[mode] = (ms, o.cpu().numpy().copy(), (L.gpu_ec_kernel_launch_count() - l0) // 13)
+        same = bool((res["1"][1] == res["0"][1]).all())
+        for mode, name in (("1", "sfold"), ("0", "table")):
+            ms = res[mode][0]
+            print(f"crc whole {n_buf} x {S}: {name}: {ms*1e3:.1f} us {n_buf*S/ms/1e6:.0f} GB/s frac={n_buf*S/ms/1e6/PEAK:.3f} launches={res[mode][2]} same={same}")
+        del t
+
+
 def rs(k, m, stripe_len, n):
     S = gpu_ec.erasure.shard_len(stripe_len, k)
     b = device.StripeBatch(n, k, m, S)
@@ -76,6 +97,8 @@ if __name__ == "__main__":
     what = sys.argv[1]
     if what == "crc":
         crc()
+    elif what == "sfold":
+        sfold()
     elif what == "rs104":
         rs(10, 4, 64 << 20, 48)
     elif what == "rs63":
