@@ -20,6 +20,7 @@
 #include "host_math.hpp"
 #include "rs_kernels.cuh"
 #include "sfold_kernels.cuh"
+#include "fused_kernels.cuh"
 
 namespace gpu_ec {
 
@@ -102,6 +103,11 @@ static int dev_prepare(Dev &d) {
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(4)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(5)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(6)));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<5, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<4, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(4, FUSED_THREADS)));
+    CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<5, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(5, FUSED_THREADS)));
+    CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<6, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(6, FUSED_THREADS)));
     CK(cudaFuncSetAttribute(crc_segments_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
     CK(cudaFuncSetAttribute(crc_segments_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
     for (auto &s : d.slots) CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
@@ -569,7 +575,7 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st);
 // finisher for n_buf buffers whose dump rows and lost-bit logs are in place: CRC the dump rows with the table
 // kernel, then fold everything into out[b * out_stride]
 static int launch_sfold_finish(Dev &d, const SfoldPlan &pl, size_t n_buf, size_t len, const uint4 *dump, const uint2 *qlog,
-                               uint32_t *dump_crc, uint32_t *out, size_t out_stride, cudaStream_t st) {
+                               uint32_t *dump_crc, uint32_t *out, size_t out_stride, cudaStream_t st, unsigned int q_group = 1) {
     const uint32_t P = kPolyReflected[0];
     CrcJob j;
     j.base = reinterpret_cast<const uint8_t *>(dump); j.n_buf = pl.n_streams; j.buf_stride = static_cast<size_t>(pl.g.dv) * 16;
@@ -579,6 +585,7 @@ static int launch_sfold_finish(Dev &d, const SfoldPlan &pl, size_t n_buf, size_t
     memset(&f, 0, sizeof f);
     f.qlog = qlog; f.dump_crc = dump_crc; f.out = out; f.out_stride = out_stride; f.n_buf = n_buf;
     f.g = pl.g;
+    f.q_group = q_group;
     f.per_thread = static_cast<unsigned int>(div_up(pl.g.ng, 256));
     f.poly_bits = P;
     f.xD = x8n_modp(16ull * pl.g.dv, P);
@@ -729,6 +736,94 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
         RET(rc);
     }
     return GPU_EC_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// fused encode + shard CRCs (fused_kernels.cuh): one pass over HBM for 8 <= k <= 12, m <= 4, IEEE.
+template <int KH>
+static cudaError_t launch_fused_x2(const FusedParams &fp, int n_clusters, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * n_clusters);
+    cfg.blockDim = dim3(FUSED_THREADS);
+    cfg.dynamicSmemBytes = fused_smem_bytes(KH, FUSED_THREADS);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, rs_lut8x2_crc_kernel<KH, FUSED_THREADS>, fp);
+}
+// n_in == 2*KH, n_out == 4 (RS(8,4), RS(10,4)): the trimmed kernel
+template <int KH>
+static cudaError_t launch_fused_fast(const FusedParams &fp, int n_clusters, cudaStream_t st) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * n_clusters);
+    cfg.blockDim = dim3(FUSED_THREADS);
+    cfg.dynamicSmemBytes = LUT_FAST_RS_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, rs_x2_crc_fast_kernel<KH, FUSED_THREADS>, fp);
+}
+
+// -> *done = false when the shape is not one the fused kernel serves (caller runs the two-pass path)
+static int encode_crc_fused(Dev &d, const gpu_ec_stripes &s, int k, int m, uint32_t *shard_crc, cudaStream_t st, bool *done) {
+    *done = false;
+    if (k <= RS_LUT8_MAX_IN || k > 2 * RS_X2_MAX_KH || m > RS_MAX_OUT || !sfold_enabled()) return GPU_EC_OK;
+    if (s.n_stripes == 0 || s.shard_len == 0 || s.n_stripes * static_cast<size_t>(k + m) >= (1ull << 32)) return GPU_EC_OK;
+    const int n = k + m;
+    const int n_clusters_max = d.sm_count / 2;
+    SfoldPlan pl;
+    if (!sfold_plan(s.n_stripes, s.shard_len, FUSED_THREADS, static_cast<size_t>(n_clusters_max), false, pl)) return GPU_EC_OK;
+    const unsigned long long n_jobs = static_cast<unsigned long long>(s.n_stripes) * pl.n_class;
+    if (n_jobs < static_cast<unsigned long long>(n_clusters_max)) return GPU_EC_OK;  // too few jobs to fill the GPU
+    std::vector<int> in(k), out(m);
+    for (int i = 0; i < k; i++) in[i] = i;
+    for (int i = 0; i < m; i++) out[i] = k + i;
+    if (!slots_addressable(s, in.data(), k, out.data(), m)) return GPU_EC_OK;
+    const Mat &M = coding_matrix(k, m);
+    const uint8_t *rows = &M[static_cast<size_t>(k) * k];
+    FusedParams fp;
+    memset(&fp, 0, sizeof fp);
+    RsParams &p = fp.rs;
+    p.base = s.base; p.shard_stride = s.shard_stride; p.stripe_stride = s.stripe_stride;
+    p.nvec = static_cast<unsigned int>(div_up(s.shard_len, 16));
+    p.n_in = k; p.n_out = m;
+    for (int r = 0; r < m; r++) { p.out_idx[r] = out[r]; p.out_off16[r] = static_cast<unsigned int>(out[r] * (s.shard_stride / 16)); }
+    for (int j = 0; j < k; j++) { p.in_idx[j] = in[j]; p.in_off16[j] = static_cast<unsigned int>(in[j] * (s.shard_stride / 16)); }
+    for (int r = 0; r < m; r++) for (int j = 0; j < k; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * k + j];
+    fp.g = pl.g;
+    fp.n_class = pl.n_class;
+    fp.n_shards = static_cast<unsigned int>(n);
+    fp.n_jobs = n_jobs;
+    sfold_tail_mask(s.shard_len, fp.tail_mask);
+    const size_t n_streams = s.n_stripes * static_cast<size_t>(n);
+    pl.n_streams = n_streams;
+    const size_t dump_bytes = n_streams * static_cast<size_t>(pl.g.dv) * 16, qlog_bytes = n_streams * static_cast<size_t>(pl.g.rseg) * pl.g.ng * 8;
+    const size_t qlog_off = round_up(dump_bytes, 256), crc_off = qlog_off + round_up(qlog_bytes, 256);
+    uint8_t *scratch = nullptr;
+    CK(cudaMallocAsync(&scratch, crc_off + 4 * n_streams, st));
+    fp.dump = reinterpret_cast<uint4 *>(scratch);
+    fp.qlog = reinterpret_cast<uint2 *>(scratch + qlog_off);
+    const int n_clusters = static_cast<int>(std::min<unsigned long long>(n_jobs, static_cast<unsigned long long>(n_clusters_max)));
+    const int kh = (k + 1) / 2;
+    static const bool generic_only = getenv("GPU_EC_FUSED_GENERIC") != nullptr;  // kernel experiments only
+    const bool fast = (k == 2 * kh) && m == RS_MAX_OUT && (kh == 4 || kh == 5) && !generic_only;
+    cudaError_t e = fast ? (kh == 4 ? launch_fused_fast<4>(fp, n_clusters, st) : launch_fused_fast<5>(fp, n_clusters, st))
+                  : kh <= 4 ? launch_fused_x2<4>(fp, n_clusters, st) : kh == 5 ? launch_fused_x2<5>(fp, n_clusters, st) : launch_fused_x2<6>(fp, n_clusters, st);
+    g_launches++;
+    int rc = GPU_EC_OK;
+    if (e != cudaSuccess) { t_last_error = std::string("fused encode+crc launch failed: ") + cudaGetErrorString(e); rc = GPU_EC_ERR_CUDA; }
+    if (rc == GPU_EC_OK)
+        rc = launch_sfold_finish(d, pl, n_streams, s.shard_len, fp.dump, fp.qlog, reinterpret_cast<uint32_t *>(scratch + crc_off), shard_crc, 1, st,
+                                 static_cast<unsigned int>(n));
+    cudaFreeAsync(scratch, st);
+    if (rc == GPU_EC_OK) *done = true;
+    return rc;
 }
 
 // CRC of the original buffer from the data-shard CRCs: constants for stripe_full_crc_kernel.
@@ -1000,8 +1095,10 @@ int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original
     const int n = k + m;
     // encode every stripe, then checksum every shard: two streaming passes. (Per-stripe-group launch
     // chains that keep the parity L2-warm were measured slower: small launches underfill the GPU.)
-    RET(encode_dev_impl(*d, *s, k, m, st));
-    {
+    bool fused = false;
+    if (poly == GPU_EC_POLY_IEEE) RET(encode_crc_fused(*d, *s, k, m, shard_crc, st, &fused));
+    if (!fused) RET(encode_dev_impl(*d, *s, k, m, st));
+    if (!fused) {
         CrcJob j;
         j.buf_stride = s->shard_stride; j.len = S; j.chunk = 0; j.poly = poly; j.out_stride = 1;
         if (s->stripe_stride == static_cast<size_t>(n) * s->shard_stride) {  // all shards at one stride

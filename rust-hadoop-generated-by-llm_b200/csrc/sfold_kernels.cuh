@@ -169,6 +169,7 @@ struct SfoldFinishParams {
     uint32_t *out;              // out[b * out_stride]
     unsigned long long out_stride, n_buf;
     SfoldGeom g;
+    unsigned int q_group;       // streams interleaved per log entry: 1 = [stream][s][g]; n = [stream / n][s][g][stream % n]
     unsigned int per_thread;    // groups per thread = ceil(ng / 256)
     uint32_t poly_bits;
     uint32_t xD, x32, y;        // x^(128*dv), x^32, x^4096
@@ -204,7 +205,8 @@ __global__ void __launch_bounds__(256) crc_sfold_finish_kernel(const __grid_cons
         uint32_t total = 0;  // crc0 of the buffer so far (thread 0 of the CTA keeps it)
         for (unsigned int seg = 0; seg < p.g.n_seg; seg++) {
             const unsigned long long stream = b * p.g.n_seg + seg;
-            const uint2 *ql = p.qlog + stream * rseg * ng;
+            const uint2 *ql = p.qlog + (stream / p.q_group) * rseg * ng * p.q_group + (stream % p.q_group);
+            const unsigned long long qs_g = p.q_group, qs_s = static_cast<unsigned long long>(ng) * p.q_group;
             uint32_t val = 0;
             for (unsigned int i = 0; i < pt; i++) {
                 const unsigned int slot = t * pt + i;
@@ -213,7 +215,7 @@ __global__ void __launch_bounds__(256) crc_sfold_finish_kernel(const __grid_cons
                     const unsigned int g = slot - off;
 #pragma unroll 4
                     for (unsigned int s = (seg ? 0u : p.g.skip_rows) + 1; s < rseg; s++) {
-                        const uint2 w = __ldg(ql + static_cast<unsigned long long>(s) * ng + g);
+                        const uint2 w = __ldg(ql + s * qs_s + g * qs_g);
                         // bits that left the group at step s: virtual words -1 (hm1) and -2 (hm2) in front of it
                         const uint32_t hm1 = (s0 ? (w.x << (32 - s0)) : 0u) ^ (s1 ? (w.x << (32 - s1)) : 0u) ^
                                              __funnelshift_r(w.x, w.y, s2) ^ __funnelshift_r(w.x, w.y, s3);

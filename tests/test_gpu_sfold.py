@@ -65,3 +65,43 @@ def test_sfold_adversarial_fills(L):
     got = _crc_dev(L, t, n_buf, stride, length, sfold=True)
     host = t.cpu().numpy().reshape(n_buf, stride)
     assert [int(c) for c in got] == [zlib.crc32(host[b, :length].tobytes()) for b in range(n_buf)]
+
+
+# ---------------------------------------------------------------- fused encode + shard CRCs (fused_kernels.cuh)
+FUSED = [(10, 4, (8 << 20) + 5, 20), (10, 4, 64 << 20, 3), (8, 3, (4 << 20) + 1, 40), (12, 4, (6 << 20) - 7, 24),
+         (10, 2, (8 << 20) + 16, 16), (9, 4, 5_000_011, 33), (11, 1, 9_999_999, 17), (8, 4, (4 << 20) + 33, 30),
+         (10, 4, 3_000_000, 75)]
+
+
+@pytest.mark.parametrize("k,m,stripe_len,n_stripes", FUSED)
+def test_fused_encode_crc_vs_oracle_and_two_pass(L, k, m, stripe_len, n_stripes):
+    """client write path dfs/client/src/mod.rs:600-611 in one pass: parity, k+m shard CRCs and CRC(original)
+    must equal the oracle's and the two-pass path's, bit for bit."""
+    import torch
+    from gpu_ec import device, erasure
+    from oracle import oracle as orc
+    S = erasure.shard_len(stripe_len, k)
+    b = device.StripeBatch(n_stripes, k, m, S)
+    b.fill_synthetic(0xEC00F05D + k, original_len=stripe_len)
+    os.environ["GPU_EC_SFOLD"] = "0"
+    crc_ref, full_ref = b.encode_crc(original_len=stripe_len)
+    torch.cuda.synchronize()
+    par_ref = b.buf[:, k:, :S].clone()
+    b.buf[:, k:] = 0x5A
+    os.environ["GPU_EC_SFOLD"] = "1"
+    l0 = L.gpu_ec_kernel_launch_count()
+    crc, full = b.encode_crc(original_len=stripe_len)
+    torch.cuda.synchronize()
+    os.environ.pop("GPU_EC_SFOLD", None)
+    assert L.gpu_ec_kernel_launch_count() - l0 <= 6, "expected the single-pass path (fused kernel + finisher launches)"
+    assert torch.equal(b.buf[:, k:, :S], par_ref)
+    assert np.array_equal(device.u32(crc), device.u32(crc_ref))
+    assert np.array_equal(device.u32(full), device.u32(full_ref))
+    crc = device.u32(crc)
+    for i in sorted({0, n_stripes - 1}):
+        data = np.concatenate([b.shard_host(i, j) for j in range(k)])
+        want = orc.encode(data, k, m)
+        for s in range(k, k + m):
+            assert np.array_equal(b.shard_host(i, s), want[s]), (i, s)
+        assert crc[i].tolist() == [zlib.crc32(x.tobytes()) for x in want]
+        assert int(device.u32(full)[i]) == zlib.crc32(data[:stripe_len].tobytes())

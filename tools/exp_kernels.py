@@ -72,6 +72,21 @@ def sfold():
         del t
 
 
+def fused(n=256):
+    """config 4 slice: RS(10,4) encode + 14 shard CRCs + CRC(original): single pass vs two-pass, and encode alone"""
+    S = gpu_ec.erasure.shard_len(64 << 20, 10)
+    b = device.StripeBatch(n, 10, 4, S)
+    b.fill_synthetic(4, original_len=64 << 20)
+    a = 14 * S * n
+    for mode, name in (("1", "fused"), ("0", "two-pass")):
+        os.environ["GPU_EC_SFOLD"] = mode
+        l0 = L.gpu_ec_kernel_launch_count()
+        ms = timed(lambda: b.encode_crc(original_len=64 << 20), 5)
+        print(f"rs(10,4)+14crc n={n} {name}: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f} launches/step={(L.gpu_ec_kernel_launch_count()-l0)//8}")
+    ms = timed(b.encode, 5)
+    print(f"rs(10,4) encode only: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
+
+
 def rs(k, m, stripe_len, n):
     S = gpu_ec.erasure.shard_len(stripe_len, k)
     b = device.StripeBatch(n, k, m, S)
@@ -99,6 +114,8 @@ if __name__ == "__main__":
         crc()
     elif what == "sfold":
         sfold()
+    elif what == "fused":
+        fused(int(sys.argv[2]) if len(sys.argv) > 2 else 256)
     elif what == "rs104":
         rs(10, 4, 64 << 20, 48)
     elif what == "rs63":
