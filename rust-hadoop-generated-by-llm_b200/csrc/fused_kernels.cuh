@@ -38,7 +38,13 @@ struct FusedParams {
     uint2 *qlog;                 // [n_stripes][rseg][ng][n_shards]: lane 0 of a warp logs its streams side by side
 };
 
-constexpr int FUSED_THREADS = 384;  // 12 warps: 168 registers per thread for 7 accumulators + two tiles of inputs
+#ifndef GPU_EC_FUSED_THREADS
+#define GPU_EC_FUSED_THREADS 384
+#endif
+#ifndef GPU_EC_SFOLD_MODE
+#define GPU_EC_SFOLD_MODE 0   // 0: funnel shifts on the alu pipe; 1: terms 2,3 as IMAD.HI + IMAD on the fma pipe
+#endif
+constexpr int FUSED_THREADS = GPU_EC_FUSED_THREADS;  // 12 warps: 168 registers per thread for 7 accumulators + two tiles of inputs
 __host__ __device__ constexpr int fused_xbuf_bytes(int nt) { return 2 * 2 * nt * 16; }
 __host__ __device__ constexpr int fused_mbar_bytes(int nt) { return 2 * 2 * (nt / 32) * 8; }
 constexpr int fused_smem_bytes(int kh, int nt) { return kh <= 4 ? LUT_FAST_RS_BYTES : kh * 256 * 32 * 4 + fused_xbuf_bytes(nt) + fused_mbar_bytes(nt); }
@@ -319,7 +325,47 @@ __device__ __forceinline__ void rs_accumulate_reload(uint4 (&d)[KH], uint32_t (&
     }
 }
 
-template <int KH, int NT>
+// all lookups of a tile with the XORs merged three at a time (one LOP3 per three table words): shards 0,1,2
+// start the accumulators, the rest are folded in; `reload(j)` is called once shard j's registers are dead
+template <int KH, typename F>
+__device__ __forceinline__ void rs_lookup_merged(uint4 (&d)[KH], uint32_t (&acc)[16], uint32_t lane4, F &&reload) {
+    static_assert(KH == 4 || KH == 5, "");
+    {
+        const uint32_t a[4] = {d[0].x, d[0].y, d[0].z, d[0].w}, b[4] = {d[1].x, d[1].y, d[1].z, d[1].w}, c[4] = {d[2].x, d[2].y, d[2].z, d[2].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            acc[q * 4 + 0] = lut_fast<0, 0>(lane4, a[q]) ^ lut_fast<1, 0>(lane4, b[q]) ^ lut_fast<2, 0>(lane4, c[q]);
+            acc[q * 4 + 1] = lut_fast<0, 1>(lane4, a[q]) ^ lut_fast<1, 1>(lane4, b[q]) ^ lut_fast<2, 1>(lane4, c[q]);
+            acc[q * 4 + 2] = lut_fast<0, 2>(lane4, a[q]) ^ lut_fast<1, 2>(lane4, b[q]) ^ lut_fast<2, 2>(lane4, c[q]);
+            acc[q * 4 + 3] = lut_fast<0, 3>(lane4, a[q]) ^ lut_fast<1, 3>(lane4, b[q]) ^ lut_fast<2, 3>(lane4, c[q]);
+        }
+        reload(0); reload(1); reload(2);
+    }
+    if constexpr (KH == 5) {
+        const uint32_t a[4] = {d[3].x, d[3].y, d[3].z, d[3].w}, b[4] = {d[4].x, d[4].y, d[4].z, d[4].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            acc[q * 4 + 0] ^= lut_fast<3, 0>(lane4, a[q]) ^ lut_fast<4, 0>(lane4, b[q]);
+            acc[q * 4 + 1] ^= lut_fast<3, 1>(lane4, a[q]) ^ lut_fast<4, 1>(lane4, b[q]);
+            acc[q * 4 + 2] ^= lut_fast<3, 2>(lane4, a[q]) ^ lut_fast<4, 2>(lane4, b[q]);
+            acc[q * 4 + 3] ^= lut_fast<3, 3>(lane4, a[q]) ^ lut_fast<4, 3>(lane4, b[q]);
+        }
+        reload(3); reload(4);
+    } else {
+        const uint32_t a[4] = {d[3].x, d[3].y, d[3].z, d[3].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            acc[q * 4 + 0] ^= lut_fast<3, 0>(lane4, a[q]);
+            acc[q * 4 + 1] ^= lut_fast<3, 1>(lane4, a[q]);
+            acc[q * 4 + 2] ^= lut_fast<3, 2>(lane4, a[q]);
+            acc[q * 4 + 3] ^= lut_fast<3, 3>(lane4, a[q]);
+        }
+        reload(3);
+    }
+}
+
+// CRC = false: the same walk and exchange as a plain apply-matrix kernel (encode, or reconstruct of 4 shards)
+template <int KH, int NT, bool CRC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fast_kernel(const __grid_constant__ FusedParams fp) {
     static_assert(KH == 4 || KH == 5, "single-PRMT layout: tables 0..3 in the two 64 KiB blocks, table 4 below them");
     extern __shared__ __align__(16) uint32_t rs_tab[];
@@ -365,6 +411,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
     const unsigned long long my_jobs = cluster < fp.n_jobs ? (fp.n_jobs - cluster + n_clusters - 1) / n_clusters : 0ull;
     const unsigned long long my_tiles = my_jobs * R;
     const unsigned int sh[4] = {fp.g.sh[0], fp.g.sh[1], fp.g.sh[2], fp.g.sh[3]};
+    const SfoldMulC mc = sfold_mul_consts(sh, lane);
     const unsigned long long lp_stride = static_cast<unsigned long long>(ng) * fp.n_shards;  // log entries per row
     unsigned int my_in_off[KH];
 #pragma unroll
@@ -397,7 +444,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
     for (int j = 0; j < KH; j++) A[j] = make_uint4(0, 0, 0, 0);
     auto crc_fast = [&](uint4 &acc, const uint4 &d, uint2 *lp) {
         if (lane == 0) *lp = make_uint2(acc.x, acc.y);
-        sfold_mul(acc, sh, lane);
+        if constexpr (GPU_EC_SFOLD_MODE == 1) sfold_mul2(acc, fp.g.sh[0], fp.g.sh[1], mc, lane);
+        else sfold_mul(acc, fp.g.sh, lane);
         xor4(acc, d);
     };
     // first row / last class / last row: threads without a vector add nothing, the ragged tail is cut at
@@ -406,7 +454,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         and4(d, ok ? 0xFFFFFFFFu : 0u);
         if (v == last_vec) { d.x &= fp.tail_mask[0]; d.y &= fp.tail_mask[1]; d.z &= fp.tail_mask[2]; d.w &= fp.tail_mask[3]; }
         if (lane == 0 && J.col) *lp = make_uint2(acc.x, acc.y);
-        sfold_mul(acc, sh, lane);
+        if constexpr (GPU_EC_SFOLD_MODE == 1) sfold_mul2(acc, fp.g.sh[0], fp.g.sh[1], mc, lane);
+        else sfold_mul(acc, fp.g.sh, lane);
         xor4(acc, d);
         if (last) {
             if (J.col) fp.dump[(static_cast<unsigned long long>(J.stripe_i) * fp.n_shards + slot) * dv + J.o] = acc;
@@ -445,23 +494,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
             *reinterpret_cast<uint4 *>(ws + static_cast<unsigned long long>(kv + own_off0) * 16ull) = o0;
             *reinterpret_cast<uint4 *>(ws + static_cast<unsigned long long>(kv + own_off1) * 16ull) = o1;
         }
-#ifndef GPU_EC_FUSED_NOCRC
-        uint2 *l2 = klp + slot_own0;
-        if (row != 0 && !JJ.lastcls && !last) {
-            crc_fast(AP0, o0, l2);
-            crc_fast(AP1, o1, l2 + 1);
-        } else {
-            crc_slow(AP0, o0, JJ, kok, kv, last, l2, slot_own0);
-            crc_slow(AP1, o1, JJ, kok, kv, last, l2 + 1, slot_own0 + 1);
+        if constexpr (CRC) {
+            uint2 *l2 = klp + slot_own0;
+            if (row != 0 && !JJ.lastcls && !last) {
+                crc_fast(AP0, o0, l2);
+                crc_fast(AP1, o1, l2 + 1);
+            } else {
+                crc_slow(AP0, o0, JJ, kok, kv, last, l2, slot_own0);
+                crc_slow(AP1, o1, JJ, kok, kv, last, l2 + 1, slot_own0 + 1);
+            }
         }
-#endif
     };
 
     for (unsigned long long ti = 0; ti < my_tiles; ti++, it++) {
         const bool last = (s + 1 == R);
         // ---- checksum the data vectors of this tile (cur is still whole)
-#ifndef GPU_EC_FUSED_NOCRC
-        {
+        if constexpr (CRC) {
             uint2 *l2 = lp + j_base;  // data slot of input j is j (encode)
             if (s != 0 && !J.lastcls && !last) {
 #pragma unroll
@@ -471,7 +519,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
                 for (int j = 0; j < KH; j++) crc_slow(A[j], cur[j], J, ok, v, last, l2 + j, static_cast<unsigned int>(j_base + j));
             }
         }
-#endif
         // ---- where the next tile is: one row down, or row 0 of the next job
         Job NJ = J;
         bool nok = J.col;
@@ -487,9 +534,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
 
         // ---- lookups; each shard's registers are refilled with the next tile as soon as they are dead
         uint32_t acc[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++) acc[i] = 0;
-        rs_accumulate_reload<KH, 0>(cur, acc, lane4, [&](int j) {
+        rs_lookup_merged<KH>(cur, acc, lane4, [&](int j) {
             if (more) cur[j] = ld_vec(nsrc + static_cast<unsigned long long>(nv + my_in_off[j]) * 16ull);
         });
         uint32_t o[4][4];  // o[q][plane]

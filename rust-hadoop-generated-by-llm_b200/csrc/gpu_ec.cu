@@ -103,8 +103,10 @@ static int dev_prepare(Dev &d) {
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(4)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(5)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(6)));
-    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
-    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<5, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<5, FUSED_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
+    CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<5, FUSED_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
     CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<4, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(4, FUSED_THREADS)));
     CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<5, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(5, FUSED_THREADS)));
     CK(cudaFuncSetAttribute(rs_lut8x2_crc_kernel<6, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, fused_smem_bytes(6, FUSED_THREADS)));
@@ -308,6 +310,8 @@ static cudaError_t launch_x2(const RsParams &p, int n_clusters, cudaStream_t st)
     return cudaLaunchKernelEx(&cfg, rs_lut8x2_kernel<KH>, p);
 }
 
+static int apply_x2_fast(Dev &d, const RsParams &rp, size_t n_stripes, cudaStream_t st);
+
 static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows, size_t row_stride, const int *in_idx,
                            int ni, const int *out_idx, int no, cudaStream_t st) {
     RsParams p;
@@ -326,6 +330,8 @@ static int launch_apply_x2(Dev &d, const gpu_ec_stripes &s, const uint8_t *rows,
         for (int j = 0; j < ni; j++) p.coef[r][j] = rows[static_cast<size_t>(r) * row_stride + j];
     const int n_clusters = static_cast<int>(std::min<unsigned long long>(p.n_tiles, static_cast<unsigned long long>(d.sm_count / 2)));
     const int kh = (ni + 1) / 2;
+    static const bool old_x2 = getenv("GPU_EC_X2_OLD") != nullptr;  // kernel experiments only
+    if (ni == 2 * kh && no == RS_MAX_OUT && (kh == 4 || kh == 5) && !old_x2) return apply_x2_fast(d, p, s.n_stripes, st);
     cudaError_t e = kh <= 4 ? launch_x2<4>(p, n_clusters, st) : kh == 5 ? launch_x2<5>(p, n_clusters, st) : launch_x2<6>(p, n_clusters, st);
     g_launches++;
     CK(e);
@@ -512,12 +518,15 @@ struct SfoldPlan {
     size_t dump_bytes = 0, qlog_bytes = 0;  // scratch, whole job
 };
 
-// knob for experiments and for the tests that pin each path: GPU_EC_SFOLD=0 keeps whole-buffer CRCs on
-// the table kernel, =1 (default) lets large aligned IEEE buffers take the sparse-fold kernels
-static bool sfold_enabled() {
+// GPU_EC_SFOLD=0 switches the sparse-fold kernels off everywhere (tests pin each path with it). The fused
+// encode + CRC pass uses them by default. Plain whole-buffer CRCs stay on the table kernel unless
+// GPU_EC_SFOLD=2: stand-alone, the sparse-fold kernel measured 0.77 of HBM peak against the table kernel's
+// 0.84 (four launches instead of two, and nothing else in the SM for its shifts to hide behind).
+static int sfold_mode() {
     const char *e = getenv("GPU_EC_SFOLD");
-    return !e || e[0] != '0';
+    return e ? atoi(e) : 1;
 }
+static bool sfold_enabled() { return sfold_mode() != 0; }
 
 // geometry for n_buf buffers of `len` bytes walked by CTAs of `tw_fixed` threads (0 = pick 256..512).
 // want_ctas = CTAs the launch can keep busy at once. false = not worth it (too short for any stride).
@@ -652,7 +661,7 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     const bool aligned = !(reinterpret_cast<uintptr_t>(j.base) & 15) && !(j.buf_stride & 15) &&
                          !(j.expect_be && (reinterpret_cast<uintptr_t>(j.expect_be) & 3));
     if (whole && aligned && j.poly == 0 && !j.expect_be && j.out && !j.no_sfold && j.len >= (256u << 10) &&
-        j.n_buf * j.len >= (8u << 20) && sfold_enabled()) {
+        j.n_buf * j.len >= (8u << 20) && sfold_mode() == 2) {
         SfoldPlan pl;
         if (sfold_plan(j.n_buf, j.len, 0, static_cast<size_t>(d.sm_count) * 2, true, pl))
             return launch_sfold_crc(d, pl, j.base, j.n_buf, j.buf_stride, j.len, j.out, j.out_stride, st);
@@ -755,7 +764,7 @@ static cudaError_t launch_fused_x2(const FusedParams &fp, int n_clusters, cudaSt
     return cudaLaunchKernelEx(&cfg, rs_lut8x2_crc_kernel<KH, FUSED_THREADS>, fp);
 }
 // n_in == 2*KH, n_out == 4 (RS(8,4), RS(10,4)): the trimmed kernel
-template <int KH>
+template <int KH, bool CRC>
 static cudaError_t launch_fused_fast(const FusedParams &fp, int n_clusters, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * n_clusters);
@@ -767,7 +776,36 @@ static cudaError_t launch_fused_fast(const FusedParams &fp, int n_clusters, cuda
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, rs_x2_crc_fast_kernel<KH, FUSED_THREADS>, fp);
+    return cudaLaunchKernelEx(&cfg, rs_x2_crc_fast_kernel<KH, FUSED_THREADS, CRC>, fp);
+}
+
+// plain apply-matrix (encode, or reconstruct of 4 shards) on the trimmed kernel: same walk, no checksums.
+// Without a CRC the row length is free: rows of n_class * FUSED_THREADS vectors, about 32 rows per job,
+// more classes (shorter jobs) when there are few stripes so that every cluster has work.
+static int apply_x2_fast(Dev &d, const RsParams &rp, size_t n_stripes, cudaStream_t st) {
+    FusedParams fp;
+    memset(&fp, 0, sizeof fp);
+    fp.rs = rp;
+    const unsigned long long nvec = rp.nvec;
+    const unsigned long long n_clusters_max = static_cast<unsigned long long>(d.sm_count / 2);
+    unsigned long long n_class = div_up(nvec, 32ull * FUSED_THREADS);
+    n_class = std::max<unsigned long long>(n_class, div_up(2 * n_clusters_max, n_stripes));
+    n_class = std::min<unsigned long long>(n_class, div_up(nvec, FUSED_THREADS));
+    const unsigned long long dv = n_class * FUSED_THREADS, R = div_up(nvec, dv);
+    fp.g.dv = static_cast<unsigned int>(dv);
+    fp.g.ng = static_cast<unsigned int>(dv / 32);
+    fp.g.rseg = static_cast<unsigned int>(R);
+    fp.g.n_seg = 1;
+    fp.g.lead = static_cast<unsigned int>(R * dv - nvec);
+    fp.n_class = static_cast<unsigned int>(n_class);
+    fp.n_shards = 1;
+    fp.n_jobs = n_stripes * n_class;
+    const int n_clusters = static_cast<int>(std::min<unsigned long long>(fp.n_jobs, n_clusters_max));
+    const int kh = rp.n_in / 2;
+    cudaError_t e = kh == 4 ? launch_fused_fast<4, false>(fp, n_clusters, st) : launch_fused_fast<5, false>(fp, n_clusters, st);
+    g_launches++;
+    CK(e);
+    return GPU_EC_OK;
 }
 
 // -> *done = false when the shape is not one the fused kernel serves (caller runs the two-pass path)
@@ -813,7 +851,7 @@ static int encode_crc_fused(Dev &d, const gpu_ec_stripes &s, int k, int m, uint3
     const int kh = (k + 1) / 2;
     static const bool generic_only = getenv("GPU_EC_FUSED_GENERIC") != nullptr;  // kernel experiments only
     const bool fast = (k == 2 * kh) && m == RS_MAX_OUT && (kh == 4 || kh == 5) && !generic_only;
-    cudaError_t e = fast ? (kh == 4 ? launch_fused_fast<4>(fp, n_clusters, st) : launch_fused_fast<5>(fp, n_clusters, st))
+    cudaError_t e = fast ? (kh == 4 ? launch_fused_fast<4, true>(fp, n_clusters, st) : launch_fused_fast<5, true>(fp, n_clusters, st))
                   : kh <= 4 ? launch_fused_x2<4>(fp, n_clusters, st) : kh == 5 ? launch_fused_x2<5>(fp, n_clusters, st) : launch_fused_x2<6>(fp, n_clusters, st);
     g_launches++;
     int rc = GPU_EC_OK;

@@ -64,6 +64,34 @@ __device__ __forceinline__ void sfold_mul(uint4 &a, const unsigned int (&sh)[4],
 }
 __device__ __forceinline__ void xor4(uint4 &a, const uint4 &d) { a.x ^= d.x; a.y ^= d.y; a.z ^= d.z; a.w ^= d.w; }
 
+// The same multiply with its work split over both integer pipes. SHF/LOP3/PRMT share the alu pipe, which
+// issues one warp instruction per two cycles per scheduler, and IMAD has the fma pipe (same rate) to itself;
+// the fused RS+CRC kernel is alu-bound (ncu: alu pipe 85 %, fma 16 %), so terms 2 and 3 are computed as
+//     funnel_r(lo, hi, k) = (lo >> k) | (hi << (32-k)) = umulhi(lo, 2^(32-k)) + hi * 2^(32-k)
+// (IMAD.HI + IMAD, no carry: the two parts have no bit in common). m2/m3 = 2^(32-k) of terms 2/3 (k & 31 must
+// not be 0: true for every stride in the table); m2n/m3n are the same for the words that come from the next
+// lane and are 0 on lane 31, which is how lane 31 shifts in zeros here.
+struct SfoldMulC { uint32_t m2, m3, m2n, m3n; };
+__device__ __forceinline__ SfoldMulC sfold_mul_consts(const unsigned int (&sh)[4], unsigned int lane) {
+    SfoldMulC c;
+    c.m2 = 1u << (32u - sh[2]);
+    c.m3 = 1u << (32u - sh[3]);
+    c.m2n = lane == 31 ? 0u : c.m2;
+    c.m3n = lane == 31 ? 0u : c.m3;
+    return c;
+}
+__device__ __forceinline__ uint32_t fsr_mul(uint32_t lo, uint32_t hi, uint32_t mlo, uint32_t mhi) { return __umulhi(lo, mlo) + hi * mhi; }
+__device__ __forceinline__ void sfold_mul2(uint4 &a, unsigned int sh0, unsigned int sh1, const SfoldMulC &c, unsigned int lane) {
+    uint32_t n0 = __shfl_down_sync(0xffffffffu, a.x, 1);
+    const uint32_t n1 = __shfl_down_sync(0xffffffffu, a.y, 1);
+    const uint32_t n0z = lane == 31 ? 0u : n0;  // the SHF terms need the zero itself
+    const uint32_t w0 = a.x, w1 = a.y, w2 = a.z, w3 = a.w;
+    a.x = __funnelshift_r(w0, w1, sh0) ^ __funnelshift_r(w0, w1, sh1) ^ fsr_mul(w1, w2, c.m2, c.m2) ^ fsr_mul(w1, w2, c.m3, c.m3);
+    a.y = __funnelshift_r(w1, w2, sh0) ^ __funnelshift_r(w1, w2, sh1) ^ fsr_mul(w2, w3, c.m2, c.m2) ^ fsr_mul(w2, w3, c.m3, c.m3);
+    a.z = __funnelshift_r(w2, w3, sh0) ^ __funnelshift_r(w2, w3, sh1) ^ fsr_mul(w3, n0, c.m2, c.m2n) ^ fsr_mul(w3, n0, c.m3, c.m3n);
+    a.w = __funnelshift_r(w3, n0z, sh0) ^ __funnelshift_r(w3, n0z, sh1) ^ fsr_mul(n0, n1, c.m2n, c.m2n) ^ fsr_mul(n0, n1, c.m3n, c.m3n);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Stand-alone streaming kernel: whole-buffer CRC partials of n_buf equally long buffers.
 // A job is (buffer, segment, class): `class` = blockDim.x consecutive columns of the row, `segment` = a

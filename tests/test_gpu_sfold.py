@@ -24,7 +24,7 @@ def L():
 
 def _crc_dev(L, t, n_buf, stride, length, sfold):
     import torch
-    os.environ["GPU_EC_SFOLD"] = "1" if sfold else "0"
+    os.environ["GPU_EC_SFOLD"] = "2" if sfold else "0"
     out = torch.zeros(n_buf, dtype=torch.int32, device="cuda")
     _lib.check(L.gpu_ec_crc32_dev(t.data_ptr(), n_buf, stride, length, 0, out.data_ptr(), torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()

@@ -61,7 +61,7 @@ def sfold():
         o = torch.empty(n_buf, dtype=torch.int32, device="cuda")
         res = {}
         for mode in ("1", "0"):
-            os.environ["GPU_EC_SFOLD"] = mode
+            os.environ["GPU_EC_SFOLD"] = "2" if mode == "1" else "0"
             l0 = L.gpu_ec_kernel_launch_count()
             ms = timed(lambda: check(L.gpu_ec_crc32_dev(t.data_ptr(), n_buf, pitch, S, 0, o.data_ptr(), st)), 10)
             res[mode] = (ms, o.cpu().numpy().copy(), (L.gpu_ec_kernel_launch_count() - l0) // 13)
