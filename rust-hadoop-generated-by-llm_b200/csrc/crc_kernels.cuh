@@ -349,6 +349,7 @@ struct FoldParams {
     int big_endian;
     const uint8_t *expect_be;
     unsigned long long *first_bad;
+    int cur_be, rag_be;                 // `cur` / `rag_src` hold byte-swapped words (a .meta array folded in place)
 };
 
 __global__ void crc_fold_kernel(const __grid_constant__ FoldParams p) {
@@ -378,7 +379,10 @@ __global__ void crc_fold_kernel(const __grid_constant__ FoldParams p) {
         const unsigned long long e = static_cast<unsigned long long>(blk) * T + tau;
         const uint32_t *src = p.cur + b * p.cur_stride_buf + oi * p.cur_group;
         uint32_t v = 0;
-        if (valid && e < cnt) v = multmodp_dev(src[cnt - 1 - e], my_c1, P);
+        if (valid && e < cnt) {
+            const uint32_t w = src[cnt - 1 - e];
+            v = multmodp_dev(p.cur_be ? bswap32(w) : w, my_c1, P);
+        }
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) v ^= __shfl_xor_sync(0xffffffffu, v, s);
         if (W > 1) {
@@ -397,8 +401,10 @@ __global__ void crc_fold_kernel(const __grid_constant__ FoldParams p) {
                 if (blk < nb_o) p.nxt[b * p.nxt_stride_buf + oi * p.nb + (nb_o - 1 - blk)] = v;
             } else {
                 uint32_t r = v;
-                if (is_last && p.last_has_rag)
-                    r = multmodp_dev(r, p.x_rag, P) ^ p.rag_src[b * p.rag_stride_buf + oi * p.rag_group + p.rag_last_cnt - 1];
+                if (is_last && p.last_has_rag) {
+                    const uint32_t w = p.rag_src[b * p.rag_stride_buf + oi * p.rag_group + p.rag_last_cnt - 1];
+                    r = multmodp_dev(r, p.x_rag, P) ^ (p.rag_be ? bswap32(w) : w);
+                }
                 if (p.out) p.out[b * p.out_stride + oi] = p.big_endian ? bswap32(r) : r;
                 if (p.expect_be) {
                     const uint32_t want = *reinterpret_cast<const uint32_t *>(p.expect_be + 4ull * oi);

@@ -436,7 +436,8 @@ static size_t fold_scratch_words(size_t n_outputs, size_t maxcnt) {
 // shorter) into one CRC per `group` segments. scratch2 (fold_scratch_words) is only touched when
 // an output has more than 1024 segments; pass nullptr to take it from the stream-ordered allocator.
 static int launch_combine(Dev &d, const uint32_t *partial, size_t n_buf, size_t segs_per_buf, size_t seg_bytes,
-                          size_t len, size_t group, const CrcJob &j, cudaStream_t st, uint32_t *scratch2 = nullptr) {
+                          size_t len, size_t group, const CrcJob &j, cudaStream_t st, uint32_t *scratch2 = nullptr,
+                          bool partial_be = false) {
     const uint32_t P = kPolyReflected[j.poly];
     FoldParams f;
     memset(&f, 0, sizeof f);
@@ -458,6 +459,7 @@ static int launch_combine(Dev &d, const uint32_t *partial, size_t n_buf, size_t 
     uint32_t *owned = nullptr;
     if (need2 && !scratch2) { CK(cudaMallocAsync(&owned, 4 * need2, st)); scratch2 = owned; }
     f.cur = partial; f.cur_stride_buf = segs_per_buf; f.cur_group = static_cast<unsigned int>(group);
+    f.cur_be = partial_be ? 1 : 0; f.rag_be = f.cur_be;  // only the first level reads the caller's array
     uint64_t U = seg_bytes;
     for (;;) {
         const size_t maxcnt = std::max(cnt_reg, cnt_last);
@@ -483,9 +485,12 @@ static int launch_combine(Dev &d, const uint32_t *partial, size_t n_buf, size_t 
         const int grid = static_cast<int>(std::min<unsigned long long>(ctas, static_cast<unsigned long long>(d.sm_count) * (2048 / block) * 4));
         crc_fold_kernel<<<grid, block, 0, st>>>(f);
         g_launches++;
-        CK(cudaGetLastError());
+        if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) {
+            if (owned) cudaFreeAsync(owned, st);
+            CK(e);
+        }
         if (f.final_level) break;
-        f.cur = scratch2; f.cur_stride_buf = f.nxt_stride_buf; f.cur_group = f.nb;
+        f.cur = scratch2; f.cur_stride_buf = f.nxt_stride_buf; f.cur_group = f.nb; f.cur_be = 0;
         scratch2 += n_outputs * f.nb;
         cnt_reg = div_up(cnt_reg, T); cnt_last = div_up(cnt_last, T);
         U *= T;
@@ -738,11 +743,15 @@ static int launch_crc(Dev &d, const CrcJob &j, cudaStream_t st) {
     if (fold32) crc_segments_kernel<true><<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     else crc_segments_kernel<false><<<grid, CRC_THREADS, CRC_SMEM_BYTES, st>>>(p);
     g_launches++;
-    CK(cudaGetLastError());
+    if (cudaError_t e = cudaGetLastError(); e != cudaSuccess) {
+        if (scratch) cudaFreeAsync(scratch, st);
+        CK(e);
+    }
     if (!direct) {
         int rc = launch_combine(d, scratch, j.n_buf, p.segs_per_buf, G, j.len, group, j, st, scratch + n_part);
-        CK(cudaFreeAsync(scratch, st));
+        cudaError_t fe = cudaFreeAsync(scratch, st);
         RET(rc);
+        CK(fe);
     }
     return GPU_EC_OK;
 }
@@ -963,7 +972,9 @@ int gpu_ec_set_devices(const int *devices, int n) {
     for (int i = 0; i < n; i++) if (devices[i] < 0 || devices[i] >= have) return GPU_EC_ERR_INVALID_ARG;
     Ctx &c = ctx();
     std::lock_guard<std::mutex> lk(c.mu);
-    c.active.assign(devices, devices + n);
+    c.active.clear();
+    for (int i = 0; i < n; i++)  // a repeated ordinal would make a batch lease the same device's slots twice and wait on itself
+        if (std::find(c.active.begin(), c.active.end(), devices[i]) == c.active.end()) c.active.push_back(devices[i]);
     return GPU_EC_OK;
 }
 
@@ -1192,7 +1203,8 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
     const size_t n_meta = div_up(S, 512);
     const size_t crc_off = static_cast<size_t>(n) * pitch;
     const size_t meta_off = crc_off + round_up(4 * static_cast<size_t>(n), 256);
-    const size_t need = meta_off + (meta_out ? 4 * n_meta * n : 0);
+    const size_t fold_off = meta_off + round_up(meta_out ? 4 * n_meta * n : 0, 256);
+    const size_t need = fold_off + (meta_out ? 4 * fold_scratch_words(n, n_meta) : 0);
     Lease L;
     RET(lease_any(L));
     RET(slot_reserve(*L.s, need));
@@ -1207,17 +1219,12 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
         CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
     }
     gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
-    RET(encode_dev_impl(*L.d, sv, k, m, st));
     const bool want_crc = shard_crc_out || full_crc_out;
+    uint32_t *d_crc = reinterpret_cast<uint32_t *>(db + crc_off);
+    bool fused = false;  // one pass for parity + shard CRCs where the fused kernel serves the shape
+    if (want_crc && !meta_out) RET(encode_crc_fused(*L.d, sv, k, m, d_crc, st, &fused));
+    if (!fused) RET(encode_dev_impl(*L.d, sv, k, m, st));
     std::vector<uint32_t> crc_tmp;
-    if (want_crc) {
-        CrcJob j;
-        j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 0;
-        j.out = reinterpret_cast<uint32_t *>(db + crc_off); j.out_stride = 1;
-        RET(launch_crc(*L.d, j, st));
-        crc_tmp.resize(n);
-        CK(cudaMemcpyAsync(crc_tmp.data(), db + crc_off, 4 * static_cast<size_t>(n), cudaMemcpyDeviceToHost, st));
-    }
     if (meta_out) {
         CrcJob j;
         j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 512;
@@ -1225,6 +1232,20 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
         RET(launch_crc(*L.d, j, st));
         for (int i = 0; i < n; i++)
             if (meta_out[i]) CK(cudaMemcpyAsync(meta_out[i], db + meta_off + 4 * n_meta * i, 4 * n_meta, cudaMemcpyDeviceToHost, st));
+        if (want_crc) {  // whole-shard CRCs folded from the .meta words: no second pass over the shards
+            CrcJob f;
+            f.poly = GPU_EC_POLY_IEEE; f.out = d_crc; f.out_stride = 1;
+            RET(launch_combine(*L.d, j.out, n, n_meta, 512, S, n_meta, f, st, reinterpret_cast<uint32_t *>(db + fold_off), true));
+        }
+    } else if (want_crc && !fused) {
+        CrcJob j;
+        j.base = db; j.n_buf = n; j.buf_stride = pitch; j.len = S; j.chunk = 0;
+        j.out = d_crc; j.out_stride = 1;
+        RET(launch_crc(*L.d, j, st));
+    }
+    if (want_crc) {
+        crc_tmp.resize(n);
+        CK(cudaMemcpyAsync(crc_tmp.data(), d_crc, 4 * static_cast<size_t>(n), cudaMemcpyDeviceToHost, st));
     }
     for (int r = 0; r < m; r++) {
         CK(cudaMemcpyAsync(shards_out[k + r], db + static_cast<size_t>(k + r) * pitch, S, cudaMemcpyDeviceToHost, st));
@@ -1635,6 +1656,12 @@ int noalloc_setup(int ordinal, NoAllocDev **out) {
         std::call_once(once, [] { for (int p = 0; p < 2; p++) crc_tables(kPolyReflected[p], tabs[p]); });
         CK(cudaMemcpyToSymbol(g_crc_tab, tabs, sizeof tabs));  // same bytes dev_prepare uploads; no allocation
         CK(cudaFuncSetAttribute(crc_segments_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CRC_SMEM_BYTES));
+        // load all three kernels this entry point can launch now (module loading is lazy, and the first launch of a
+        // kernel is where its code gets device memory): no later call, on whichever path, triggers a load
+        cudaFuncAttributes fa;
+        CK(cudaFuncGetAttributes(&fa, crc_segments_kernel<false>));
+        CK(cudaFuncGetAttributes(&fa, crc_fold_kernel));
+        CK(cudaFuncGetAttributes(&fa, crc_chunks_slow_kernel));
         nd.scratch = static_cast<uint32_t *>(addr);
         nd.shim.ordinal = ordinal;
         nd.shim.sm_count = sms;
@@ -1681,8 +1708,10 @@ int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_strid
     // shortest segment (most parallelism) whose per-segment CRCs, plus the few words the fold needs
     // beyond 1024 segments per buffer, fit the fixed array
     auto words_for = [&](size_t g) { const size_t segs = div_up(len, g); return n_buf * segs + fold_scratch_words(n_buf, segs); };
-    size_t G = 512;
-    while (G <= NOALLOC_MAX_SEGMENT && words_for(G) > NOALLOC_MAX_PARTIALS) G *= 2;
+    // start from the segment length gpu_ec_crc32_dev would pick (tiles fill whole waves of the GPU), then grow it
+    // until the partials fit
+    size_t G = pick_whole_segment(nd->shim, n_buf, len);
+    while (G <= NOALLOC_MAX_SEGMENT && words_for(G) > NOALLOC_MAX_PARTIALS) G = round_up(G * 2, 128);
     if (G > NOALLOC_MAX_SEGMENT) {
         char msg[256];
         snprintf(msg, sizeof msg,

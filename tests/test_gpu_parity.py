@@ -648,6 +648,27 @@ def test_two_devices_in_one_process(L, orc):
         _lib.check(L.gpu_ec_set_devices(one, 1))
 
 
+def test_set_devices_ignores_repeated_ordinals(L, orc):
+    """{0, 0} must not make a batch lease device 0's slots twice (it would wait on itself forever)."""
+    devs = (C.c_int * 2)(0, 0)
+    _lib.check(L.gpu_ec_set_devices(devs, 2))
+    try:
+        k, m, stripe_len, n = 4, 2, 100_000, 5
+        S = erasure.shard_len(stripe_len, k)
+        data = orc.fill_synthetic(stripe_len * n, 0xEC0000D3)
+        parity = np.empty((n, m, S), np.uint8)
+        done = []
+        th = threading.Thread(target=lambda: done.append(L.gpu_ec_encode_batch(data.ctypes.data, stripe_len, n, k, m, parity.ctypes.data, None, None)))
+        th.start()
+        th.join(timeout=60)
+        assert not th.is_alive(), "batch call hung on a repeated device ordinal"
+        assert done == [0]
+        assert np.array_equal(parity[0], orc.encode(data[:stripe_len], k, m)[k:])
+    finally:
+        one = (C.c_int * 1)(0)
+        _lib.check(L.gpu_ec_set_devices(one, 1))
+
+
 def test_reconstruct_ec_shard_repair_path(L, orc, tmp_path):
     """chunkserver.rs:503-640 after the fetch: rebuild the target shard and store it with its .meta."""
     store = checksum.BlockStore(str(tmp_path))

@@ -105,3 +105,24 @@ def test_fused_encode_crc_vs_oracle_and_two_pass(L, k, m, stripe_len, n_stripes)
             assert np.array_equal(b.shard_host(i, s), want[s]), (i, s)
         assert crc[i].tolist() == [zlib.crc32(x.tobytes()) for x in want]
         assert int(device.u32(full)[i]) == zlib.crc32(data[:stripe_len].tobytes())
+
+
+@pytest.mark.parametrize("k,m,n", [(10, 4, (64 << 20) + 3), (6, 3, 20_000_003), (10, 4, 1_000_001)])
+def test_host_encode_with_checksums_all_paths(L, k, m, n):
+    """gpu_ec_encode through host pointers: (a) shard CRCs only -> the fused pass where the shape allows it,
+    (b) with .meta arrays -> whole-shard CRCs folded from the per-512-byte CRCs (no extra pass). Both against
+    the oracle (dfs/client/src/mod.rs:600-611; dfs/chunkserver/src/chunkserver.rs:182-196)."""
+    from gpu_ec import erasure
+    from oracle import oracle as orc
+    data = orc.fill_synthetic(n, 0xEC00A0A0 + k)
+    want = orc.encode(data, k, m)
+    want_crc = [zlib.crc32(s.tobytes()) for s in want]
+    for with_meta in (False, True):
+        shards, crcs, full, metas = erasure.encode_with_checksums(data, k, m, with_meta=with_meta)
+        for i in range(k + m):
+            assert np.array_equal(shards[i], want[i]), (with_meta, i)
+        assert crcs.tolist() == want_crc, with_meta
+        assert full == zlib.crc32(data.tobytes())
+        if with_meta:
+            for i in (0, k - 1, k, k + m - 1):
+                assert metas[i].tobytes() == orc.meta_encode_be(orc.crc32_chunks(want[i]))

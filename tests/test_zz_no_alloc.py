@@ -73,3 +73,39 @@ def test_noalloc_rejects_sizes_beyond_the_built_in_scratch():
     assert b"built-in scratch" in L.gpu_ec_last_error()
     assert L.gpu_ec_kernel_launch_count() == before
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("n_buf,length", [(1, 600 << 20), (14, 160 << 20), (3, (96 << 20) + 77)])
+def test_noalloc_long_segments(n_buf, length):
+    """Inputs whose per-segment CRCs do not fit the array at the usual segment length: the entry point
+    lengthens the segments (up to 64 KiB, longer than gpu_ec_crc32_dev ever uses) instead of allocating.
+    Same answer as the existing entry point, spot-checked against zlib."""
+    import torch
+    L = gpu_ec.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    stride = (length + 255) // 256 * 256
+    free, _ = torch.cuda.mem_get_info()
+    if n_buf * stride + (1 << 30) > free:
+        pytest.skip("not enough free device memory")
+    t = torch.empty(n_buf * stride, dtype=torch.uint8, device="cuda")
+    _lib.check(L.gpu_ec_fill_synthetic_dev(t.data_ptr(), t.numel(), 0xEC0000F2 + n_buf, 0, st))
+    want, got = _both(L, torch, t, n_buf, stride, length)
+    assert np.array_equal(got, want)
+    b = n_buf - 1
+    assert int(got[b]) == zlib.crc32(t[b * stride:b * stride + length].cpu().numpy().tobytes())
+
+
+def test_noalloc_very_long_segments_when_memory_allows():
+    """>= 17 GiB in one call: 32 KiB .. 64 KiB segments. Needs ~18 GiB free; skipped otherwise."""
+    import torch
+    L = gpu_ec.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    n_buf, length = 17, 1 << 30
+    free, _ = torch.cuda.mem_get_info()
+    if n_buf * length + (2 << 30) > free:
+        pytest.skip("not enough free device memory")
+    t = torch.empty(n_buf * length, dtype=torch.uint8, device="cuda")
+    _lib.check(L.gpu_ec_fill_synthetic_dev(t.data_ptr(), t.numel(), 0xEC0000F3, 0, st))
+    want, got = _both(L, torch, t, n_buf, length, length)
+    assert np.array_equal(got, want)
+    assert int(got[16]) == zlib.crc32(t[16 * length:].cpu().numpy().tobytes())
