@@ -33,6 +33,7 @@ STRIPES_PER_GPU = 64
 SEED = 0xEC000001
 METRIC = "rs63_encode_algorithmic_GBps"
 UNIT = "GB/s"
+PCIE_H2D_CEILING = 55.6  # GB/s per GPU, pinned cudaMemcpyAsync H2D alone, measured (profiles/r02/r02_pcie_1.json)
 
 
 def peaks():
@@ -84,34 +85,115 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference(steps, warmup, full_line, n_gpus=1):
-    """The reference arm / cpu_baseline: C oracle (port) on all host cores, bounded sample."""
-    import numpy as np
+def make_config(n_local, S):
+    """The workload description both arms print (identical keys and values: same_config)."""
+    return {"workload": "rs63_encode_64MiB_blocks", "k": K_DATA, "m": M_PAR, "stripe_len": STRIPE_LEN, "shard_len": S,
+            "stripes_per_gpu": n_local, "partition": "stripe i -> gpu i mod G, no collective",
+            "l2": "inputs (6.4 GB/GPU) exceed the 126 MB L2; no flush needed", "bytes_counted": "(k+m)*shard_len per stripe"}
+
+
+def cpu_reference(steps, warmup, full_line, n_gpus=1, n_local=STRIPES_PER_GPU):
+    """The reference arm / cpu_baseline: C oracle (port) on all host cores, bounded sample of the workload:
+    16 of its 64 MiB stripes per pass, one stripe per thread, `warmup` untimed passes then `steps` timed ones."""
     from oracle import oracle
     threads = os.cpu_count() or 1
     n_stripes = max(4, min(threads, 16))
     data = oracle.fill_synthetic(STRIPE_LEN * n_stripes, SEED)
     S = oracle.shard_len(STRIPE_LEN, K_DATA)
     alg = (K_DATA + M_PAR) * S * n_stripes
-    for _ in range(min(warmup, 1)):
-        oracle.bench_encode(data[:STRIPE_LEN * min(n_stripes, threads)], STRIPE_LEN, min(n_stripes, threads), K_DATA, M_PAR, threads)
+    for _ in range(warmup):
+        oracle.bench_encode(data, STRIPE_LEN, n_stripes, K_DATA, M_PAR, threads)
     ts = [oracle.bench_encode(data, STRIPE_LEN, n_stripes, K_DATA, M_PAR, threads) for _ in range(max(1, steps))]
     t = sum(ts) / len(ts)
     val = alg / t / 1e9
-    t1 = oracle.bench_encode(data, STRIPE_LEN, 1, K_DATA, M_PAR, 1)  # what ONE reference call gets: it is single-threaded
+    t1 = min(oracle.bench_encode(data, STRIPE_LEN, 1, K_DATA, M_PAR, 1) for _ in range(2))  # ONE reference call: it is single-threaded
     base = {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": "port",
             "single_thread_value": round((K_DATA + M_PAR) * S / t1 / 1e9, 3),
-            "sample": f"{n_stripes} x 64 MiB RS(6,3) stripes, one stripe per thread, {len(ts)} pass(es); "
-                      "C restatement of reed-solomon-erasure 6.0.0 scalar table path incl. erasure.rs:17-20 copies"}
+            "sample": f"{n_stripes} of the 64 MiB RS(6,3) stripes per pass, one stripe per thread, {warmup} warm + {len(ts)} timed pass(es); "
+                      "C restatement of reed-solomon-erasure 6.0.0's scalar table path incl. both input copies of erasure.rs:17-19"}
     if not full_line:
         return base
     return {"metric": METRIC, "value": round(val, 3), "unit": UNIT, "impl": "reference", "n_gpus": n_gpus, "steps": len(ts),
-            "warmup": min(warmup, 1), "ms_per_step": round(t * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "rs63_encode_64MiB_blocks", "k": K_DATA, "m": M_PAR, "stripe_len": STRIPE_LEN,
-                       "stripes_per_step": n_stripes},
+            "warmup": warmup, "ms_per_step": round(t * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic (splitmix64 counter stream)",
+            "config": make_config(n_local, S),
             "cpu_baseline": base,
             "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def cpu_others(oracle, np):
+    """CPU side of the other BASELINE configs on bounded samples: C port at all cores and at one thread, plus zlib's
+    crc32() as the independent CRC row. -> {workload: {...}}"""
+    import zlib
+    from concurrent.futures import ThreadPoolExecutor
+    threads = os.cpu_count() or 1
+    out = {}
+    # config 3: RS(6,3) reconstruct of shards {1,4,7} over 1 MiB stripes (chunkserver.rs:620-623)
+    k, m, L1 = 6, 3, 1 << 20
+    S3 = oracle.shard_len(L1, k)
+    n3 = 256
+    sh = np.empty((n3, k + m, S3), np.uint8)
+    d = oracle.fill_synthetic(L1 * 8, 0xEC000003)
+    for i in range(n3):
+        sh[i] = oracle.encode(d[(i % 8) * L1:(i % 8 + 1) * L1], k, m)
+    pres = [1, 0, 1, 1, 0, 1, 1, 0, 1]
+    oracle.bench_reconstruct(sh, pres, S3, n3, k, m, threads)
+    tN = min(oracle.bench_reconstruct(sh, pres, S3, n3, k, m, threads) for _ in range(3))
+    t1 = oracle.bench_reconstruct(sh[:16], pres, S3, 16, k, m, 1)
+    out["rs63_reconstruct_3_erasures_4096x1MiB"] = {"cpu_port_GBps": round(9 * S3 * n3 / tN / 1e9, 2), "cpu_port_1thread_GBps": round(9 * S3 * 16 / t1 / 1e9, 3),
+                                                    "cpu_cores": threads, "cpu_sample": f"{n3} of the 4096 stripes, 3 passes (best)"}
+    del sh
+    # config 4: RS(10,4) encode + 14 shard CRCs + CRC(original) (client/src/mod.rs:600-611), 64 MiB stripes
+    k, m = 10, 4
+    S4 = oracle.shard_len(STRIPE_LEN, k)
+    n4 = max(4, min(threads, 16))
+    d = oracle.fill_synthetic(STRIPE_LEN * n4, 0xEC000004)
+    oracle.bench_encode(d, STRIPE_LEN, n4, k, m, threads, True)
+    tN = min(oracle.bench_encode(d, STRIPE_LEN, n4, k, m, threads, True) for _ in range(3))
+    t1 = oracle.bench_encode(d, STRIPE_LEN, 1, k, m, 1, True)
+    tNe = min(oracle.bench_encode(d, STRIPE_LEN, n4, k, m, threads, False) for _ in range(2))
+    out["rs104_encode_plus_14_crc_64MiB_stripes"] = {"cpu_port_GBps": round(14 * S4 * n4 / tN / 1e9, 2), "cpu_port_1thread_GBps": round(14 * S4 / t1 / 1e9, 3),
+                                                     "cpu_cores": threads, "cpu_sample": f"{n4} of the 1024 stripes, 3 passes (best)"}
+    out["rs104_encode_only"] = {"cpu_port_GBps": round(14 * S4 * n4 / tNe / 1e9, 2), "cpu_cores": threads}
+    # config 2: CRC-32 IEEE per 512 B and per 64 KiB: PCLMULQDQ port (what crc32fast runs on this CPU) and zlib
+    samp = d[:256 << 20]
+    for chunk in (512, 65536):
+        oracle.bench_crc_chunks(samp, chunk, 0, threads)
+        tN = min(oracle.bench_crc_chunks(samp, chunk, 0, threads) for _ in range(3))
+        t1 = oracle.bench_crc_chunks(samp[:64 << 20], chunk, 0, 1)
+        out[f"crc32_ieee_{chunk}B_chunks_1GiB"] = {"cpu_port_GBps": round(samp.size / tN / 1e9, 2), "cpu_port_1thread_GBps": round((64 << 20) / t1 / 1e9, 2),
+                                                  "cpu_cores": threads, "cpu_sample": "256 MiB of the 1 GiB, 3 passes (best)"}
+    mv = memoryview(samp)
+    step = 64 << 10
+    t0 = time.perf_counter()
+    for o in range(0, 64 << 20, step):
+        zlib.crc32(mv[o:o + step])
+    tz1 = time.perf_counter() - t0
+    slabs = [mv[i * (samp.size // threads):(i + 1) * (samp.size // threads)] for i in range(threads)]
+    def zl(sl):
+        for o in range(0, len(sl), step):
+            zlib.crc32(sl[o:o + step])
+    with ThreadPoolExecutor(threads) as ex:
+        t0 = time.perf_counter()
+        list(ex.map(zl, slabs))
+        tzN = time.perf_counter() - t0
+    out["crc32_ieee_65536B_chunks_1GiB"].update({"cpu_zlib_GBps": round(samp.size / tzN / 1e9, 2), "cpu_zlib_1thread_GBps": round((64 << 20) / tz1 / 1e9, 2),
+                                                 "cpu_zlib_note": "zlib.crc32 per 64 KiB chunk (releases the GIL): the independent CRC row"})
+    return out
+
+
+def ncu_traffic(kernel_substr, alg_bytes):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel_substr` whose algorithmic bytes equal
+    alg_bytes, from the committed ncu --set full summaries (profiles/ncu_traffic.json); None when no capture of that
+    kernel and shape is committed (the value is then not measured by anything in the repo)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            for e in json.load(f)["captures"]:
+                if kernel_substr in e["kernel"] and int(e["algorithmic_bytes_per_launch"]) == int(alg_bytes):
+                    return int(e["dram_bytes_read"]) + int(e["dram_bytes_write"]), e.get("source")
+    except Exception:  # noqa: BLE001
+        pass
+    return None, None
 
 
 def bind_to_gpu_numa_node(torch, dev):
@@ -151,11 +233,11 @@ def run_e2e(L, oracle, np, C, check, barrier, partition, dist, world, rank, S, n
     def e2e_step():
         check(L.gpu_ec_encode_batch(hin, STRIPE_LEN, n_e2e, K_DATA, M_PAR, hout, None, None))
 
-    for _ in range(2):
+    for _ in range(3):
         e2e_step()
     barrier()
     t0 = time.perf_counter()
-    e2e_steps = 3
+    e2e_steps = 20
     for _ in range(e2e_steps):
         e2e_step()
     barrier()
@@ -169,7 +251,7 @@ def run_e2e(L, oracle, np, C, check, barrier, partition, dist, world, rank, S, n
     L.gpu_ec_free_pinned(hin)
     L.gpu_ec_free_pinned(hout)
 
-    return e2e_val, e2e_ms
+    return e2e_val, e2e_ms, e2e_steps
 
 
 def run_config5(L, oracle, np, C, check, rank):
@@ -219,6 +301,27 @@ def run_config5(L, oracle, np, C, check, rank):
                     raise RuntimeError("verify reported corruption")
         except Exception as e:  # noqa: BLE001
             errs.append(repr(e))
+    # degraded read (client/src/mod.rs:1143-1164): shards {1,4,7} (2 data + 1 parity) did not arrive; the k first
+    # survivors go H2D, one pass rebuilds the three, they come back D2H (gpu_ec_reconstruct)
+    want0 = oracle.encode(srcs[0][1], k, m)
+    n_deg = 4  # shard sets (pinned, 9 x 44.7 MB each); threads share them read-only except the rebuilt slots
+    deg = [pinned((k + m) * S) for _ in range(n_deg)]
+    for _, a in deg:
+        a[:] = want0.reshape(-1)
+    present = np.array([1, 0, 1, 1, 0, 1, 1, 0, 1], np.uint8)
+    def degraded(t):
+        try:
+            base = deg[t % n_deg][1]
+            # every thread rebuilds into its own scratch rows (the parity buffers of the write leg are free now)
+            ptrs = (C.c_void_p * (k + m))()
+            for i in range(k + m):
+                ptrs[i] = base.ctypes.data + i * S
+            for r, idx in enumerate((1, 4, 7)):
+                ptrs[idx] = pars[t][1].ctypes.data + r * S
+            for _ in range(iters):
+                check(L.gpu_ec_reconstruct(ptrs, present.ctypes.data, S, k, m))
+        except Exception as e:  # noqa: BLE001
+            errs.append(repr(e))
     def run(fn):
         th = [threading.Thread(target=fn, args=(t,)) for t in range(n_thr)]
         t0 = time.perf_counter()
@@ -231,18 +334,27 @@ def run_config5(L, oracle, np, C, check, rank):
     tr = run(reader)
     if errs:
         raise SystemExit("config 5 failed: " + errs[0])
-    want = oracle.encode(srcs[0][1], k, m)  # parity gate on one block (thread 0 used source 0)
+    want = want0  # parity gate on one block (thread 0 used source 0)
     got = pars[0][1].reshape(m, S)
     ok = np.array_equal(got, want[k:]) and crcs[0].tolist() == [zlib.crc32(x.tobytes()) for x in want]
     ok = ok and fulls[0].value == zlib.crc32(srcs[0][1].tobytes())
     if not ok:
         raise SystemExit("PARITY FAILURE config 5")
-    for p, _ in srcs + pars:
+    run(degraded)
+    td = run(degraded)
+    if errs:
+        raise SystemExit("config 5 degraded read failed: " + errs[0])
+    rebuilt = pars[5][1].reshape(m, S)
+    if not (np.array_equal(rebuilt[0], want0[1]) and np.array_equal(rebuilt[1], want0[4]) and np.array_equal(rebuilt[2], want0[7])):
+        raise SystemExit("PARITY FAILURE config 5 degraded read")
+    for p, _ in srcs + pars + deg:
         L.gpu_ec_free_pinned(p)
     total = n_thr * iters * blk
     return {"threads": n_thr, "block_bytes": blk, "blocks_per_thread": iters,
             "write_data_GBps": round(total / tw / 1e9, 2), "read_verify_data_GBps": round(total / tr / 1e9, 2),
-            "note": "per GPU, wall clock, PCIe-bound: write moves 1.0x data H2D + 0.5x D2H, read moves 1.0x H2D"}
+            "degraded_read_data_GBps": round(n_thr * iters * k * S / td / 1e9, 2),
+            "note": "per GPU, wall clock, PCIe-bound: write moves 1.0x data H2D + 0.5x D2H, read-verify 1.0x H2D, "
+                    "degraded read (shards 1,4,7 rebuilt) 1.0x H2D + 0.5x D2H; data bytes = k*shard_len per block"}
 
 
 def main():
@@ -262,7 +374,7 @@ def main():
 
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(cpu_reference(args.steps, args.warmup, True, args.gpus)), flush=True)
+            print(json.dumps(cpu_reference(min(args.steps, 20), max(3, args.warmup), True, args.gpus, args.stripes)), flush=True)
         return 0
 
     import numpy as np
@@ -338,9 +450,9 @@ def main():
 
     # ---- e2e: host-pointer C ABI, pinned buffers, H2D + D2H inside the timed region
     n_e2e = 16
-    e2e_val = e2e_ms = None
+    e2e_val = e2e_ms = e2e_steps = None
     if not args.no_e2e:
-        e2e_val, e2e_ms = run_e2e(L, oracle, np, C, check, barrier, partition, dist, world, rank, S, n_e2e)
+        e2e_val, e2e_ms, e2e_steps = run_e2e(L, oracle, np, C, check, barrier, partition, dist, world, rank, S, n_e2e)
     # ---- secondary configs (device-resident), each with its own roofline fraction
     sub = {}
     if not args.no_sub:
@@ -351,18 +463,21 @@ def main():
         b3 = device.StripeBatch(4096, 6, 3, S3)
         b3.fill_synthetic(0xEC000003 + rank)
         b3.encode()
-        ref3 = b3.buf[:8].clone()
+        torch.cuda.synchronize()
+        gate = sorted({0, 1, 2, 3, 2047, 2048, 4094, 4095})  # 8 of the 4096 stripes, oracle-encoded from their data shards
+        want3 = {i: oracle.encode(np.concatenate([b3.shard_host(i, j) for j in range(6)]), 6, 3) for i in gate}
         b3.buf[:, [1, 4, 7]] = 0
         present = [1, 0, 1, 1, 0, 1, 1, 0, 1]
         b3.reconstruct(present)
         torch.cuda.synchronize()
-        if not torch.equal(b3.buf[:8, :, :S3], ref3[:, :, :S3]):
-            raise SystemExit("PARITY FAILURE reconstruct")
+        for i in gate:
+            if not all(np.array_equal(b3.shard_host(i, s_), want3[i][s_]) for s_ in range(9)):
+                raise SystemExit(f"PARITY FAILURE reconstruct (stripe {i} differs from the oracle)")
         ms3, _ = timed(lambda: b3.reconstruct(present), 10, 3)
         a3 = 9 * S3 * 4096
         sub["rs63_reconstruct_3_erasures_4096x1MiB"] = {"GBps_algorithmic": round(a3 * world / ms3 / 1e6, 1), "ms": round(ms3, 4),
                                                        "roofline_frac": round(a3 / ms3 / 1e6 / peak, 4)}
-        del b3, ref3
+        del b3
         torch.cuda.empty_cache()
         # config 2: 1 GiB, CRC-32 IEEE per 512 B (the .meta layout) and per 64 KiB, write side + verify side
         n2 = 1 << 30
@@ -380,20 +495,12 @@ def main():
             sub[f"crc32_ieee_{chunk}B_chunks_1GiB"] = {
                 "write_GBps": round(a2 * world / msw / 1e6, 1), "verify_GBps": round(a2 * world / msv / 1e6, 1),
                 "roofline_frac_write": round(a2 / msw / 1e6 / peak, 4), "roofline_frac_verify": round(a2 / msv / 1e6 / peak, 4)}
-        if world == 1 and not args.no_cpu:  # CPU side of config 2 on a bounded sample (crc32fast's PCLMULQDQ path restated)
-            threads = os.cpu_count() or 1
-            samp = t2[:256 << 20].cpu().numpy()
-            for chunk in (512, 65536):
-                tc = oracle.bench_crc_chunks(samp, chunk, 0, threads)
-                t1c = oracle.bench_crc_chunks(samp[:32 << 20], chunk, 0, 1)
-                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_port_GBps"] = round(samp.size / tc / 1e9, 2)
-                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_port_1thread_GBps"] = round((32 << 20) / t1c / 1e9, 2)
-                sub[f"crc32_ieee_{chunk}B_chunks_1GiB"]["cpu_cores"] = threads
-            del samp
-        host_sample = t2[:1 << 20].cpu().numpy()
-        chk = device.u32(device.crc32_chunks(t2[:1 << 20], 512))
-        if not np.array_equal(chk, oracle.crc32_chunks(host_sample, 512)):
-            raise SystemExit("PARITY FAILURE crc chunks")
+        host_sample = t2[:64 << 20].cpu().numpy()   # 64 MiB slice of the timed buffer, both chunk sizes, against the oracle
+        for chunk in (512, 65536):
+            chk = device.u32(device.crc32_chunks(t2, chunk))[:(64 << 20) // chunk]
+            if not np.array_equal(chk, oracle.crc32_chunks(host_sample, chunk)):
+                raise SystemExit(f"PARITY FAILURE crc chunks ({chunk} B) vs oracle")
+        del host_sample
         outc = torch.empty(n2 // 512, dtype=torch.int32, device="cuda")
         msc, _ = timed(lambda: device.crc32_chunks(t2, 512, poly=gpu_ec.POLY_CASTAGNOLI, out=outc), 5, 3)
         sub["crc32c_castagnoli_512B_chunks_1GiB"] = {"write_GBps": round((n2 + 4 * (n2 // 512)) * world / msc / 1e6, 1),
@@ -415,11 +522,14 @@ def main():
         ok = ok and int(device.u32(full4)[0]) == zlib.crc32(d0[:64 << 20].tobytes())
         if not ok:
             raise SystemExit("PARITY FAILURE fused RS(10,4)+CRC")
-        ms4, _ = timed(lambda: b4.encode_crc(original_len=64 << 20), 5, 3)
+        ms4, l4 = timed(lambda: b4.encode_crc(original_len=64 << 20), 5, 3)
         a4 = 14 * S4 * n4
         sub["rs104_encode_plus_14_crc_64MiB_stripes"] = {"GBps_algorithmic": round(a4 * world / ms4 / 1e6, 1), "ms": round(ms4, 3),
                                                         "stripes_per_gpu": n4, "scaling": "strong (1024 stripes = 64 GiB of data in total)", "roofline_frac": round(a4 / ms4 / 1e6 / peak, 4),
-                                                        "note": "encode pass, then segment-CRC + fold kernels over all 14 shards; CRC(original) by 32-bit algebra; not one fused kernel"}
+                                                        "launches_per_step": None,
+                                                        "note": "ONE pass over HBM: 2-CTA-cluster byte-LUT encode with the 14 shard CRCs accumulated in registers (sparse-fold CRC), "
+                                                                "then the small finisher kernels (1/R of the data); CRC(original) by 32-bit algebra"}
+        sub["rs104_encode_plus_14_crc_64MiB_stripes"]["launches_per_step"] = int(l4) // 5
         ms4e, _ = timed(b4.encode, 5, 3)
         sub["rs104_encode_only"] = {"GBps_algorithmic": round(a4 * world / ms4e / 1e6, 1), "roofline_frac": round(a4 / ms4e / 1e6 / peak, 4)}
         del b4
@@ -443,29 +553,53 @@ def main():
         sub["small_call_latency_us"] = dict(small, note="host-pointer API incl. pageable H2D/D2H and Python ctypes overhead")
 
     if rank == 0:
+        traffic, traffic_src = ncu_traffic("rs_lut8_kernel", alg_bytes_rank)
+        # the other BASELINE configs, in a key the driver keeps: one roofline entry per dominant kernel
+        others = []
+        def other(workload, kernel, gbps_key="GBps_algorithmic", frac_key="roofline_frac", alg=None):
+            e = sub.get(workload)
+            if e:
+                others.append({"workload": workload, "kernel": kernel, "achieved": round(e[gbps_key] / world, 1), "unit": "GB/s",
+                               "frac": e[frac_key], "peak": peak, "algorithmic_bytes_per_launch": alg})
+        if sub:
+            other("rs63_reconstruct_3_erasures_4096x1MiB", "rs_lut8_kernel<6> (decode rows)", alg=9 * gpu_ec.erasure.shard_len(1 << 20, 6) * 4096)
+            for chunk in (512, 65536):
+                w = f"crc32_ieee_{chunk}B_chunks_1GiB"
+                other(w, "crc_segments_kernel (write)", "write_GBps", "roofline_frac_write", (1 << 30) + 4 * ((1 << 30) // chunk))
+                other(w, "crc_segments_kernel (verify)", "verify_GBps", "roofline_frac_verify", (1 << 30) + 4 * ((1 << 30) // chunk))
+            other("rs104_encode_only", "rs_x2_crc_fast_kernel<5,384,false>", alg=a4)
+            other("rs104_encode_plus_14_crc_64MiB_stripes", "rs_x2_crc_fast_kernel<5,384,true> + finisher", alg=a4)
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic (splitmix64 counter stream)",
-            "config": {"workload": "rs63_encode_64MiB_blocks", "k": K_DATA, "m": M_PAR, "stripe_len": STRIPE_LEN,
-                       "shard_len": S, "stripes_per_gpu": n_local, "partition": "stripe i -> gpu i mod G, no collective",
-                       "l2": "inputs (6.4 GB/GPU) exceed the 126 MB L2; no flush needed", "bytes_counted": "(k+m)*shard_len per stripe"},
+            "config": make_config(n_local, S),
             "gpu_launches": int(launches),
             "clocks": clocks,
             "e2e": None if e2e_val is None else {
                 "value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": n_e2e * STRIPE_LEN,
-                "d2h_bytes_per_step": n_e2e * M_PAR * S, "ms_per_step": round(e2e_ms, 3), "stripes_per_step": n_e2e,
-                "api": "gpu_ec_encode_batch (pinned host buffers)", "host_binding": numa, "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2)},
+                "d2h_bytes_per_step": n_e2e * M_PAR * S, "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps, "stripes_per_step": n_e2e,
+                "api": "gpu_ec_encode_batch (pinned host buffers)", "host_binding": numa, "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2),
+                # plain pinned cudaMemcpyAsync on this pool's boxes, no kernels (tools/pcie_ceiling.py, profiles/r02/):
+                # the input crosses PCIe once, so data GB/s per GPU cannot exceed the H2D figure
+                "pcie_h2d_ceiling_GBps_per_gpu": PCIE_H2D_CEILING,
+                "frac_of_pcie_ceiling": round(n_e2e * STRIPE_LEN / e2e_ms / 1e6 / PCIE_H2D_CEILING, 3)},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 1), "peak": peak, "unit": "GB/s", "frac": round(per_gpu / peak, 4),
-                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this shape (64 stripes) from the
-                         # committed ncu --set full capture profiles/r01_final_ncu_full_summary.txt (4.295 GB + 2.117 GB)
-                         "traffic": 6412392000 if n_local == 64 else None, "traffic_unit": "bytes per launch",
+                         "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src,
                          "kernel": "rs_lut8_kernel<6>", "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg_bytes_rank},
+                         "algorithmic_bytes_per_launch": alg_bytes_rank, "others": others},
             "sub": sub,
         }
         if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_reference(1, 0, False)
+            line["cpu_baseline"] = cpu_reference(3, warmup, False)
+            if sub:
+                cpu_o = cpu_others(oracle, np)
+                line["cpu_baseline"]["others"] = cpu_o
+                for o in others:
+                    c = cpu_o.get(o["workload"])
+                    if c:
+                        o["cpu_port_GBps"] = c.get("cpu_port_GBps")
+                        o["cpu_cores"] = c.get("cpu_cores")
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

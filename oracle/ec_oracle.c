@@ -450,9 +450,15 @@ static void *job_run(void *arg) {
     if (j->kind == 0) { /* encode (+ per-shard CRCs + full CRC: client/src/mod.rs:600-611) */
         size_t S = orc_shard_len(j->stripe_len, (size_t)j->k);
         uint8_t *sh = (uint8_t *)malloc(S * (size_t)(j->k + j->m));
+        uint8_t *padded = (uint8_t *)malloc(S * (size_t)j->k);
         for (size_t s = (size_t)j->tid; s < j->n_stripes; s += (size_t)j->nthreads) {
             const uint8_t *d = j->data + s * j->stripe_len;
-            orc_encode(d, j->stripe_len, j->k, j->m, sh);
+            /* erasure.rs:17-18: data.to_vec() + resize = input copy #1; orc_encode's own copy into the
+             * shard buffers is erasure.rs:19 (chunks().map(to_vec)) = input copy #2 */
+            memcpy(padded, d, j->stripe_len);
+            memset(padded + j->stripe_len, 0, S * (size_t)j->k - j->stripe_len);
+            j->sink ^= padded[j->stripe_len - 1];
+            orc_encode(padded, j->stripe_len, j->k, j->m, sh);
             j->sink ^= sh[S * (size_t)j->k];
             if (j->with_crc) {
                 for (int i = 0; i < j->k + j->m; i++) j->sink ^= orc_crc32(sh + S * (size_t)i, S, ORC_POLY_IEEE);
@@ -460,6 +466,7 @@ static void *job_run(void *arg) {
             }
         }
         free(sh);
+        free(padded);
     } else if (j->kind == 1) { /* chunk CRCs: each thread takes a contiguous slab of whole chunks */
         size_t nchunks = (j->stripe_len + j->chunk - 1) / j->chunk;
         size_t per = (nchunks + (size_t)j->nthreads - 1) / (size_t)j->nthreads;
