@@ -33,7 +33,11 @@ STRIPES_PER_GPU = 64
 SEED = 0xEC000001
 METRIC = "rs63_encode_algorithmic_GBps"
 UNIT = "GB/s"
-PCIE_H2D_CEILING = 55.6  # GB/s per GPU, pinned cudaMemcpyAsync H2D alone, measured (profiles/r02/r02_pcie_1.json)
+# Plain pinned cudaMemcpyAsync on this pool's boxes, no kernels, N processes at once (tools/pcie_ceiling.py;
+# profiles/r02/r02_pcie_{1,2,4,8}.json): aggregate GB/s over the N GPUs for H2D alone and for H2D + D2H together.
+# The VM's host side, not the library, sets the e2e scaling curve: 8 GPUs together get 225 GB/s H2D but only
+# 151 GB/s when both directions run, 4 GPUs 115 / 102.
+PCIE_CEILING = {1: {"h2d": 55.6, "both": 91.5}, 2: {"h2d": 111.2, "both": 153.5}, 4: {"h2d": 115.3, "both": 101.8}, 8: {"h2d": 225.5, "both": 150.7}}
 
 
 def peaks():
@@ -580,10 +584,10 @@ def main():
                 "value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": n_e2e * STRIPE_LEN,
                 "d2h_bytes_per_step": n_e2e * M_PAR * S, "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps, "stripes_per_step": n_e2e,
                 "api": "gpu_ec_encode_batch (pinned host buffers)", "host_binding": numa, "data_GBps": round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6, 2),
-                # plain pinned cudaMemcpyAsync on this pool's boxes, no kernels (tools/pcie_ceiling.py, profiles/r02/):
-                # the input crosses PCIe once, so data GB/s per GPU cannot exceed the H2D figure
-                "pcie_h2d_ceiling_GBps_per_gpu": PCIE_H2D_CEILING,
-                "frac_of_pcie_ceiling": round(n_e2e * STRIPE_LEN / e2e_ms / 1e6 / PCIE_H2D_CEILING, 3)},
+                # e2e `value` = (data + parity) bytes / time = all bytes that crossed PCIe per second
+                "pcie_ceiling_GBps_aggregate": PCIE_CEILING.get(world),
+                "frac_of_h2d_ceiling": None if world not in PCIE_CEILING else round(n_e2e * STRIPE_LEN * world / e2e_ms / 1e6 / PCIE_CEILING[world]["h2d"], 3),
+                "frac_of_bidirectional_ceiling": None if world not in PCIE_CEILING else round(e2e_val / PCIE_CEILING[world]["both"], 3)},
             "roofline": {"bound": "hbm", "achieved": round(per_gpu, 1), "peak": peak, "unit": "GB/s", "frac": round(per_gpu / peak, 4),
                          "traffic": traffic, "traffic_unit": "bytes per launch", "traffic_source": traffic_src,
                          "kernel": "rs_lut8_kernel<6>", "peak_source": peak_src,
