@@ -15,6 +15,7 @@
 #include <vector>
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include "crc_kernels.cuh"
 #include "host_math.hpp"
@@ -42,6 +43,22 @@ static std::atomic<uint64_t> g_launches{0};
         int rc_ = (call);           \
         if (rc_ != GPU_EC_OK) return rc_; \
     } while (0)
+
+// NVTX range around every compute entry point (the reference wraps its RPCs in tracing spans,
+// dfs/chunkserver/src/chunkserver.rs:727-728; here the spans show up in nsys/ncu timelines). Header-only
+// NVTX3: without a profiler attached a push/pop is one predictable branch.
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+#define GPU_EC_TRACE() NvtxRange nvtx_range_(__func__)
+// the _dev entry points work on whichever device owns the caller's pointer: they switch to it for their launches
+// and put the caller's current device back on return
+struct DeviceGuard {
+    int prev = -1;
+    DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); } }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 
 static inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 static inline size_t div_up(size_t a, size_t b) { return (a + b - 1) / b; }
@@ -1061,6 +1078,8 @@ uint64_t gpu_ec_kernel_launch_count(void) { return g_launches.load(); }
 // device-resident entry points
 
 int gpu_ec_encode_dev(const gpu_ec_stripes *s, int k, int m, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     RET(check_km(k, m));
     RET(check_stripes(s));
     Dev *d;
@@ -1069,6 +1088,8 @@ int gpu_ec_encode_dev(const gpu_ec_stripes *s, int k, int m, void *stream) {
 }
 
 int gpu_ec_reconstruct_dev(const gpu_ec_stripes *s, const uint8_t *present, int k, int m, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!present) return GPU_EC_ERR_INVALID_ARG;
     DecodePlan plan;
     bool noop = false;
@@ -1084,6 +1105,8 @@ int gpu_ec_reconstruct_dev(const gpu_ec_stripes *s, const uint8_t *present, int 
 
 int gpu_ec_apply_matrix_dev(const gpu_ec_stripes *s, const uint8_t *rows, const int *in_idx, int n_in,
                             const int *out_idx, int n_out, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!rows || !in_idx || !out_idx || n_in <= 0 || n_out <= 0 || n_in > 256 || n_out > 256) return GPU_EC_ERR_INVALID_ARG;
     RET(check_stripes(s));
     Dev *d;
@@ -1093,6 +1116,8 @@ int gpu_ec_apply_matrix_dev(const gpu_ec_stripes *s, const uint8_t *rows, const 
 
 int gpu_ec_crc32_chunks_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, size_t chunk,
                             int poly, uint32_t *out, size_t out_stride, int big_endian, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!base || !out || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     Dev *d;
     RET(dev_of_ptr(base, &d));
@@ -1104,6 +1129,8 @@ int gpu_ec_crc32_chunks_dev(const uint8_t *base, size_t n_buf, size_t buf_stride
 
 int gpu_ec_crc32_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, int poly, uint32_t *out,
                      void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!base || !out || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     Dev *d;
     RET(dev_of_ptr(base, &d));
@@ -1115,6 +1142,8 @@ int gpu_ec_crc32_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_
 
 int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int poly, const uint8_t *meta_be,
                              long long *first_bad, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!data || !meta_be || !first_bad || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     Dev *d;
     RET(dev_of_ptr(data, &d));
@@ -1132,6 +1161,8 @@ int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int 
 
 int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original_len, int poly,
                           uint32_t *shard_crc, uint32_t *full_crc, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     RET(check_km(k, m));
     RET(check_stripes(s));
     if (!shard_crc || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
@@ -1174,6 +1205,8 @@ int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original
 }
 
 int gpu_ec_fill_synthetic_dev(uint8_t *out, size_t len, uint64_t seed, uint64_t byte_offset, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!out) return GPU_EC_ERR_INVALID_ARG;
     if ((reinterpret_cast<uintptr_t>(out) & 7) || (byte_offset & 7)) return GPU_EC_ERR_UNALIGNED;
     if (len == 0) return GPU_EC_OK;
@@ -1192,6 +1225,7 @@ int gpu_ec_fill_synthetic_dev(uint8_t *out, size_t len, uint64_t seed, uint64_t 
 
 int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const *shards_out,
                   uint32_t *shard_crc_out, uint32_t *full_crc_out, uint8_t *const *meta_out) {
+    GPU_EC_TRACE();
     if (k <= 0 || m <= 0) return GPU_EC_ERR_ZERO_SHARDS;   // erasure.rs:8-10 (checked first there too)
     if (len == 0) return GPU_EC_ERR_EMPTY_DATA;            // erasure.rs:11-13
     if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;    // ReedSolomon::new
@@ -1265,6 +1299,7 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
 }
 
 int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m) {
+    GPU_EC_TRACE();
     if (!shards || !present) return GPU_EC_ERR_INVALID_ARG;
     DecodePlan plan;
     bool noop = false;
@@ -1296,6 +1331,7 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
 
 int gpu_ec_reconstruct_only(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m,
                             const int *want, int n_want) {
+    GPU_EC_TRACE();
     if (!shards || !present || !want || n_want <= 0) return GPU_EC_ERR_INVALID_ARG;
     DecodePlan plan;
     bool noop = false;
@@ -1334,6 +1370,7 @@ int gpu_ec_reconstruct_only(uint8_t *const *shards, const uint8_t *present, size
 
 int gpu_ec_decode(uint8_t *const *shards, uint8_t *present, size_t shard_len, int k, int m, size_t original_len,
                   uint8_t *out) {
+    GPU_EC_TRACE();
     if (!shards || !present || (!out && original_len)) return GPU_EC_ERR_INVALID_ARG;
     RET(gpu_ec_reconstruct(shards, present, shard_len, k, m));
     for (int i = 0; i < k + m; i++) present[i] = 1;
@@ -1400,11 +1437,13 @@ static int crc_host_common(const uint8_t *data, size_t len, size_t chunk, int po
 }
 
 int gpu_ec_crc32(const uint8_t *data, size_t len, int poly, uint32_t *out) {
+    GPU_EC_TRACE();
     if (!out || (!data && len) || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     return crc_host_common(data, len, 0, poly, out, nullptr, nullptr, nullptr);
 }
 
 int gpu_ec_crc32_chunks(const uint8_t *data, size_t len, size_t chunk, int poly, uint32_t *out) {
+    GPU_EC_TRACE();
     if ((!out && len) || (!data && len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     if (len == 0) { RET(ensure_init()); return GPU_EC_OK; }  // zero chunks, empty .meta (chunkserver.rs:184)
     return crc_host_common(data, len, chunk, poly, nullptr, out, nullptr, nullptr);
@@ -1412,6 +1451,7 @@ int gpu_ec_crc32_chunks(const uint8_t *data, size_t len, size_t chunk, int poly,
 
 int gpu_ec_verify_chunks(const uint8_t *data, size_t len, size_t chunk, int poly, const uint8_t *meta_be,
                          size_t meta_len, int64_t *first_bad) {
+    GPU_EC_TRACE();
     if ((!data && len) || (!meta_be && meta_len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     if (first_bad) *first_bad = -1;
     RET(ensure_init());
@@ -1423,6 +1463,7 @@ int gpu_ec_verify_chunks(const uint8_t *data, size_t len, size_t chunk, int poly
 
 int gpu_ec_block_checksums(const uint8_t *data, size_t len, size_t chunk, int poly, uint32_t *whole_crc_out,
                            uint32_t *chunk_crc_out) {
+    GPU_EC_TRACE();
     if ((!data && len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     if (len == 0) { RET(ensure_init()); if (whole_crc_out) *whole_crc_out = 0; return GPU_EC_OK; }
     return crc_host_common(data, len, chunk, poly, whole_crc_out, chunk_crc_out, nullptr, nullptr);
@@ -1457,6 +1498,7 @@ struct BatchLanes {
 
 int gpu_ec_encode_batch(const uint8_t *data, size_t stripe_len, size_t n_stripes, int k, int m,
                         uint8_t *parity_out, uint32_t *shard_crc_out, uint32_t *full_crc_out) {
+    GPU_EC_TRACE();
     if (k <= 0 || m <= 0) return GPU_EC_ERR_ZERO_SHARDS;
     if (stripe_len == 0) return GPU_EC_ERR_EMPTY_DATA;
     if (k + m > 256) return GPU_EC_ERR_TOO_MANY_SHARDS;
@@ -1511,6 +1553,7 @@ int gpu_ec_encode_batch(const uint8_t *data, size_t stripe_len, size_t n_stripes
 }
 
 int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t shard_len, size_t n_stripes, int k, int m) {
+    GPU_EC_TRACE();
     if (!shards || !present) return GPU_EC_ERR_INVALID_ARG;
     DecodePlan plan;
     bool noop = false;
@@ -1552,6 +1595,7 @@ int gpu_ec_reconstruct_batch(uint8_t *shards, const uint8_t *present, size_t sha
 int gpu_ec_verify_chunks_batch(size_t n_blocks, const uint8_t *const *data, const size_t *lens, size_t chunk, int poly,
                                const uint8_t *const *meta_be, const size_t *meta_lens, int *status_out,
                                int64_t *first_bad_out) {
+    GPU_EC_TRACE();
     if ((n_blocks && (!data || !lens || !meta_be || !meta_lens || !status_out)) || chunk == 0 || (poly != 0 && poly != 1))
         return GPU_EC_ERR_INVALID_ARG;
     if (n_blocks == 0) return GPU_EC_OK;
@@ -1674,6 +1718,8 @@ int noalloc_setup(int ordinal, NoAllocDev **out) {
 
 int gpu_ec_crc32_dev_noalloc(const uint8_t *base, size_t n_buf, size_t buf_stride, size_t len, int poly,
                              uint32_t *out, void *stream) {
+    GPU_EC_TRACE();
+    DeviceGuard device_guard_;
     if (!base || !out || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     cudaPointerAttributes attr;
     CK(cudaPointerGetAttributes(&attr, base));
