@@ -555,6 +555,29 @@ def main():
                 fn()
             small[name] = round((time.perf_counter() - t0) / 50 * 1e6, 1)
         sub["small_call_latency_us"] = dict(small, note="host-pointer API incl. pageable H2D/D2H and Python ctypes overhead")
+        # many small WriteBlocks (chunkserver.rs:746-769 + :195 each): one batched call vs one call per block vs the CPU port
+        bb = {}
+        for size, nb in ((4096, 512), (65536, 512), (1 << 20, 128)):
+            blocks = [oracle.fill_synthetic(size, 100 + i) for i in range(nb)]
+            _ck.block_checksums_batch(blocks)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                wb, cb = _ck.block_checksums_batch(blocks)
+            tb = (time.perf_counter() - t0) / 3
+            t0 = time.perf_counter()
+            for b_ in blocks[:64]:
+                _ck.block_checksums(b_)
+            t1 = (time.perf_counter() - t0) / 64
+            t0 = time.perf_counter()
+            for b_ in blocks[:64]:
+                oracle.crc32(b_)
+                oracle.crc32_chunks(b_)
+            tc = (time.perf_counter() - t0) / 64
+            if int(wb[0]) != oracle.crc32(blocks[0]) or not np.array_equal(cb[-1], oracle.crc32_chunks(blocks[-1])):
+                raise SystemExit("PARITY FAILURE batched block checksums")
+            bb[f"{size}B"] = {"batched_blocks_per_s": round(nb / tb), "single_call_blocks_per_s": round(1 / t1), "cpu_port_1thread_blocks_per_s": round(1 / tc),
+                              "blocks_per_batch": nb}
+        sub["block_checksums_batch"] = dict(bb, note="gpu_ec_block_checksums_batch: pageable host blocks, one CRC launch + one fold launch + one sync per batch")
 
     if rank == 0:
         traffic, traffic_src = ncu_traffic("rs_lut8_kernel", alg_bytes_rank)

@@ -92,7 +92,8 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
 /* The repair path's variant (chunkserver.rs:503-640 keeps only opt_shards[shard_index] of what
  * reconstruct rebuilt): rebuild ONLY the absent slots listed in want[n_want] (one pass over the first
  * k present shards, n_want outputs); other absent slots are left untouched. Same errors as
- * gpu_ec_reconstruct; a wanted slot that is present or out of range is GPU_EC_ERR_INVALID_ARG. */
+ * gpu_ec_reconstruct; a wanted slot that is present or out of range is GPU_EC_ERR_INVALID_ARG.
+ * shards[i] of an absent slot that is not wanted is never dereferenced and may be NULL. */
 int gpu_ec_reconstruct_only(uint8_t *const *shards, const uint8_t *present, size_t shard_len, int k, int m,
                             const int *want, int n_want);
 /* erasure.rs:30-49 decode(): reconstruct, then concatenate shards[0..k) truncated to original_len.
@@ -114,6 +115,14 @@ int gpu_ec_verify_chunks(const uint8_t *data, size_t len, size_t chunk, int poly
  * whole-block CRC and the per-chunk array from a single H2D. Either output may be NULL. */
 int gpu_ec_block_checksums(const uint8_t *data, size_t len, size_t chunk, int poly,
                            uint32_t *whole_crc_out, uint32_t *chunk_crc_out);
+/* The same for n blocks of different lengths in one go (a chunkserver taking many sub-MiB WriteBlocks,
+ * chunkserver.rs:746-769 + :195 per block): one H2D per block into one staging buffer, ONE CRC launch over
+ * every chunk of every block, one small launch that repairs short last chunks and folds the whole-block
+ * CRCs (per-block offsets in a device array), one synchronisation. whole_crc_out: n words or NULL;
+ * chunk_crc_out: n pointers (ceil(lens[b]/chunk) words each; entries may be NULL) or NULL. chunk must be a
+ * multiple of 128 up to 1024 for the one-launch path (512 in the reference); other sizes run block by block. */
+int gpu_ec_block_checksums_batch(size_t n, const uint8_t *const *data, const size_t *lens, size_t chunk, int poly,
+                                 uint32_t *whole_crc_out, uint32_t *const *chunk_crc_out);
 
 /* Batches of equal-sized stripes laid out back to back in (ideally pinned) host memory;
  * stripes are independent and are pipelined over streams and spread round-robin over the
@@ -138,6 +147,8 @@ int gpu_ec_verify_chunks_batch(size_t n_blocks, const uint8_t *const *data, cons
                                int *status_out, int64_t *first_bad_out);
 
 /* ---- device-resident entry points (device pointers, stream = cudaStream_t) --------------- */
+/* They only enqueue work on `stream` and never synchronise. The device that owns the pointer is used:
+ * the call makes it current for its launches and restores the caller's current device before returning. */
 /* n_stripes stripes of k+m shard slots in device memory:
  * slot s of stripe i starts at base + i*stripe_stride + s*shard_stride and holds shard_len bytes.
  * base and both strides must be multiples of 16 and shard_stride >= round_up(shard_len, 16):
@@ -175,11 +186,15 @@ int gpu_ec_crc32_dev(const uint8_t *base, size_t n_buf, size_t buf_stride, size_
  * words; *first_bad (device int64) receives the first differing chunk index or -1. */
 int gpu_ec_verify_chunks_dev(const uint8_t *data, size_t len, size_t chunk, int poly,
                              const uint8_t *meta_be, long long *first_bad, void *stream);
-/* encode + CRC-32 of all k+m shards (+ CRC of the original original_len bytes when full_crc is
- * non-NULL; original_len = 0 means k*shard_len) for every stripe (an encode pass, then a CRC pass
- * over all shards; full_crc costs no data pass). shard_crc: n_stripes*(k+m) words; full_crc: n_stripes.
- * The bytes of the data slots beyond original_len must be the zero padding of erasure.rs:18
- * (full_crc is derived from the shard CRCs with that assumption, not from a second data pass). */
+/* The client write sequence dfs/client/src/mod.rs:600-611 (encode, a CRC per shard, a CRC of the
+ * original) for every stripe: parity + CRC-32 of all k+m shards (+ CRC of the original original_len
+ * bytes when full_crc is non-NULL; original_len = 0 means k*shard_len). shard_crc: n_stripes*(k+m) words;
+ * full_crc: n_stripes. For 8 <= k <= 12, m <= 4, poly = IEEE and shards of a few hundred KiB or more this is
+ * ONE pass over HBM: the shard CRCs are accumulated in registers inside the encode kernel (fused_kernels.cuh)
+ * and finished by two small kernels over ~4 % of the data; it takes stream-ordered scratch
+ * (cudaMallocAsync on `stream`) of about 4.5 % of the stripes' size. Other shapes run an encode pass and a
+ * CRC pass. full_crc never costs a data pass: it is derived from the shard CRCs, which is why the bytes of
+ * the data slots beyond original_len must be the zero padding of erasure.rs:18. */
 int gpu_ec_encode_crc_dev(const gpu_ec_stripes *s, int k, int m, size_t original_len, int poly,
                           uint32_t *shard_crc, uint32_t *full_crc, void *stream);
 /* No counterpart in the reference. Same result as gpu_ec_crc32_dev (whole-buffer CRC of each of

@@ -441,6 +441,72 @@ __global__ void stripe_full_crc_kernel(const FullCrcParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Batched small-block checksums (many WriteBlocks in one go: chunkserver.rs:746-769 + :195 per block).
+// The blocks sit back to back in one staging buffer, each starting on a chunk boundary and zero-padded to
+// one, so ONE crc_segments launch hashes every chunk of every block; this kernel then, per block (one CTA),
+//   * repairs the CRC of a short last chunk, which was hashed with its zero padding:
+//       crc(A) = (crc(A || 0^p) ^ crc(0^chunk)) * x^(-8p) ^ crc(0^r),   r = |A|, p = chunk - r
+//   * folds the chunk CRCs into the whole-block CRC: crc(A||B) = crc(A) * x^(8|B|) ^ crc(B).
+struct BlockDesc {
+    unsigned long long first_chunk;  // index of the block's first chunk CRC in `crcs`
+    unsigned int n_full;             // full chunks
+    unsigned int rag;                // bytes of the short last chunk (0 = none)
+    uint32_t x_inv_pad;              // x^(-8*(chunk - rag))
+    uint32_t cz_rag;                 // crc(zeros(rag))
+    uint32_t x_rag;                  // x^(8*rag)
+    uint32_t pad_;
+};
+struct BlocksFinishParams {
+    const BlockDesc *desc;
+    unsigned long long n_blocks;
+    uint32_t *crcs;       // chunk CRCs of all blocks, repaired in place
+    uint32_t *whole;      // [n_blocks] or null
+    uint32_t cz_chunk;    // crc(zeros(chunk))
+    uint32_t x_chunk;     // x^(8*chunk)
+    uint32_t poly_bits;
+};
+__global__ void __launch_bounds__(128) crc_blocks_finish_kernel(const __grid_constant__ BlocksFinishParams p) {
+    __shared__ uint32_t z[8], wsum[4];
+    const unsigned int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t P = p.poly_bits;
+    for (unsigned long long b = blockIdx.x; b < p.n_blocks; b += gridDim.x) {
+        const BlockDesc d = p.desc[b];
+        const unsigned int pt = (d.n_full + 127u) / 128u;  // full chunks per thread, right-aligned over 128*pt slots
+        __syncthreads();
+        if (t == 0) {  // tree constants z[L] = X^(pt * 2^L), X = x^(8*chunk)
+            uint32_t r = 0x80000000u, sq = p.x_chunk;
+            for (unsigned int e = pt; e; e >>= 1) { if (e & 1u) r = multmodp_dev(sq, r, P); sq = multmodp_dev(sq, sq, P); }
+            for (int L = 0; L < 7; L++) { z[L] = r; r = multmodp_dev(r, r, P); }
+        }
+        __syncthreads();
+        const unsigned int off = pt * 128u - d.n_full;
+        uint32_t val = 0;
+        for (unsigned int i = 0; i < pt; i++) {
+            const unsigned int slot = t * pt + i;
+            val = multmodp_dev(val, p.x_chunk, P);
+            if (slot >= off) val ^= p.crcs[d.first_chunk + (slot - off)];
+        }
+#pragma unroll
+        for (int L = 0; L < 5; L++) {
+            const uint32_t left = __shfl_up_sync(0xffffffffu, val, 1u << L);
+            if ((lane & ((2u << L) - 1u)) == (2u << L) - 1u) val ^= multmodp_dev(left, z[L], P);
+        }
+        if (lane == 31) wsum[warp] = val;
+        __syncthreads();
+        if (t == 0) {
+            uint32_t w = 0;
+            for (int i = 0; i < 4; i++) w = multmodp_dev(w, z[5], P) ^ wsum[i];  // z[5] = X^(32*pt): one warp further
+            if (d.rag) {
+                const uint32_t c = multmodp_dev(p.crcs[d.first_chunk + d.n_full] ^ p.cz_chunk, d.x_inv_pad, P) ^ d.cz_rag;
+                p.crcs[d.first_chunk + d.n_full] = c;
+                w = multmodp_dev(w, d.x_rag, P) ^ c;
+            }
+            if (p.whole) p.whole[b] = w;
+        }
+    }
+}
+
 __global__ void first_bad_finish_kernel(unsigned long long *first_bad) {
     if (*first_bad == 0xFFFFFFFFFFFFFFFFull) *reinterpret_cast<long long *>(first_bad) = -1;
 }

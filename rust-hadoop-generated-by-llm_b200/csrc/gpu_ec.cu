@@ -69,6 +69,8 @@ struct Slot {
     cudaStream_t stream = nullptr;
     uint8_t *dbuf = nullptr;
     size_t cap = 0;
+    uint8_t *hbuf = nullptr;   // pinned host staging (batched small blocks: one H2D / one D2H per batch)
+    size_t hcap = 0;
     bool busy = false;
 };
 struct Dev {
@@ -257,6 +259,15 @@ static int slot_reserve(Slot &s, size_t bytes) {
     CK(cudaMalloc(&s.dbuf, want));
     CK(cudaMemsetAsync(s.dbuf, 0, want, s.stream));
     s.cap = want;
+    return GPU_EC_OK;
+}
+
+static int slot_reserve_host(Slot &s, size_t bytes) {
+    if (s.hcap >= bytes) return GPU_EC_OK;
+    if (s.hbuf) { CK(cudaStreamSynchronize(s.stream)); CK(cudaFreeHost(s.hbuf)); s.hbuf = nullptr; s.hcap = 0; }
+    const size_t want = round_up(bytes + bytes / 4, 1 << 20);
+    CK(cudaHostAlloc(reinterpret_cast<void **>(&s.hbuf), want, cudaHostAllocPortable));
+    s.hcap = want;
     return GPU_EC_OK;
 }
 
@@ -971,6 +982,7 @@ void gpu_ec_shutdown(void) {
         for (auto &s : d.slots) {
             if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); s.stream = nullptr; }
             if (s.dbuf) { cudaFree(s.dbuf); s.dbuf = nullptr; s.cap = 0; }
+            if (s.hbuf) { cudaFreeHost(s.hbuf); s.hbuf = nullptr; s.hcap = 0; }
         }
         d.ready = false;
     }
@@ -1467,6 +1479,110 @@ int gpu_ec_block_checksums(const uint8_t *data, size_t len, size_t chunk, int po
     if ((!data && len) || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
     if (len == 0) { RET(ensure_init()); if (whole_crc_out) *whole_crc_out = 0; return GPU_EC_OK; }
     return crc_host_common(data, len, chunk, poly, whole_crc_out, chunk_crc_out, nullptr, nullptr);
+}
+
+int gpu_ec_block_checksums_batch(size_t n, const uint8_t *const *data, const size_t *lens, size_t chunk, int poly,
+                                 uint32_t *whole_crc_out, uint32_t *const *chunk_crc_out) {
+    GPU_EC_TRACE();
+    if (n == 0) { RET(ensure_init()); return GPU_EC_OK; }
+    if (!data || !lens || chunk == 0 || (poly != 0 && poly != 1)) return GPU_EC_ERR_INVALID_ARG;
+    for (size_t b = 0; b < n; b++) if (!data[b] && lens[b]) return GPU_EC_ERR_INVALID_ARG;
+    if (chunk % 128 || chunk > 1024) {  // chunk sizes the one-launch layout does not serve: block by block
+        for (size_t b = 0; b < n; b++)
+            RET(gpu_ec_block_checksums(data[b], lens[b], chunk, poly, whole_crc_out ? whole_crc_out + b : nullptr,
+                                       chunk_crc_out ? chunk_crc_out[b] : nullptr));
+        return GPU_EC_OK;
+    }
+    const uint32_t P = kPolyReflected[poly];
+    // layout: blocks back to back, each starting on a chunk boundary (so chunk i of the staging buffer is a chunk
+    // of exactly one block); a short last chunk is hashed with its zero padding and repaired afterwards
+    std::vector<BlockDesc> desc(n);
+    std::vector<size_t> off(n);
+    size_t total = 0, n_chunks = 0;
+    for (size_t b = 0; b < n; b++) {
+        off[b] = total;
+        BlockDesc &d = desc[b];
+        memset(&d, 0, sizeof d);
+        d.first_chunk = n_chunks;
+        d.n_full = static_cast<unsigned int>(lens[b] / chunk);
+        d.rag = static_cast<unsigned int>(lens[b] % chunk);
+        if (d.rag) {
+            d.x_inv_pad = xinv8n_modp(chunk - d.rag, P);
+            d.cz_rag = crc_of_zeros(d.rag, P);
+            d.x_rag = x8n_modp(d.rag, P);
+        }
+        const size_t nc = div_up(lens[b], chunk);
+        if (lens[b] / chunk >= (1ull << 32)) return GPU_EC_ERR_INVALID_ARG;
+        n_chunks += nc;
+        total += nc * chunk;
+    }
+    const size_t crc_off = round_up(std::max<size_t>(total, 256), 256);
+    const size_t desc_off = crc_off + round_up(4 * n_chunks + 4, 256);
+    const size_t whole_off = desc_off + round_up(sizeof(BlockDesc) * n, 256);
+    const size_t need = whole_off + round_up(4 * n, 256);
+    Lease L;
+    RET(lease_any(L));
+    RET(slot_reserve(*L.s, need));
+    cudaStream_t st = L.s->stream;
+    uint8_t *db = L.s->dbuf;
+    // small batches are packed on the host into pinned staging: one H2D for all blocks (and one D2H for all CRCs)
+    // instead of a copy per block; large ones copy block by block straight from the caller's memory
+    const bool packed = total <= (64u << 20);
+    if (packed) {
+        RET(slot_reserve_host(*L.s, std::max(total, 4 * n_chunks + 4 * n)));
+        for (size_t b = 0; b < n; b++) {
+            if (lens[b]) memcpy(L.s->hbuf + off[b], data[b], lens[b]);
+            const size_t pad = div_up(lens[b], chunk) * chunk - lens[b];
+            if (pad) memset(L.s->hbuf + off[b] + lens[b], 0, pad);
+        }
+        if (total) CK(cudaMemcpyAsync(db, L.s->hbuf, total, cudaMemcpyHostToDevice, st));
+    } else {
+        for (size_t b = 0; b < n; b++) {
+            if (!lens[b]) continue;
+            CK(cudaMemcpyAsync(db + off[b], data[b], lens[b], cudaMemcpyHostToDevice, st));
+            const size_t pad = div_up(lens[b], chunk) * chunk - lens[b];
+            if (pad) CK(cudaMemsetAsync(db + off[b] + lens[b], 0, pad, st));
+        }
+    }
+    CK(cudaMemcpyAsync(db + desc_off, desc.data(), sizeof(BlockDesc) * n, cudaMemcpyHostToDevice, st));
+    uint32_t *d_crc = reinterpret_cast<uint32_t *>(db + crc_off);
+    uint32_t *d_whole = reinterpret_cast<uint32_t *>(db + whole_off);
+    if (n_chunks) {
+        CrcJob j;  // ONE launch over every chunk of every block
+        j.base = db; j.n_buf = 1; j.buf_stride = crc_off; j.len = total; j.chunk = chunk; j.poly = poly;
+        j.out = d_crc; j.out_stride = n_chunks;
+        RET(launch_crc(*L.d, j, st));
+    }
+    BlocksFinishParams f;
+    memset(&f, 0, sizeof f);
+    f.desc = reinterpret_cast<const BlockDesc *>(db + desc_off);
+    f.n_blocks = n; f.crcs = d_crc; f.whole = d_whole;
+    f.cz_chunk = crc_of_zeros(chunk, P); f.x_chunk = x8n_modp(chunk, P); f.poly_bits = P;
+    const int grid = static_cast<int>(std::min<size_t>(n, static_cast<size_t>(L.d->sm_count) * 8));
+    crc_blocks_finish_kernel<<<grid, 128, 0, st>>>(f);
+    g_launches++;
+    CK(cudaGetLastError());
+    if (packed) {  // hbuf was copied to the device before the kernels ran on this stream: it can take the results now
+        uint32_t *h_crc = reinterpret_cast<uint32_t *>(L.s->hbuf), *h_whole = h_crc + n_chunks;
+        if (chunk_crc_out && n_chunks) CK(cudaMemcpyAsync(h_crc, d_crc, 4 * n_chunks, cudaMemcpyDeviceToHost, st));
+        if (whole_crc_out) CK(cudaMemcpyAsync(h_whole, d_whole, 4 * n, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (whole_crc_out) memcpy(whole_crc_out, h_whole, 4 * n);
+        if (chunk_crc_out)
+            for (size_t b = 0; b < n; b++) {
+                const size_t nc = div_up(lens[b], chunk);
+                if (nc && chunk_crc_out[b]) memcpy(chunk_crc_out[b], h_crc + desc[b].first_chunk, 4 * nc);
+            }
+        return GPU_EC_OK;
+    }
+    if (whole_crc_out) CK(cudaMemcpyAsync(whole_crc_out, d_whole, 4 * n, cudaMemcpyDeviceToHost, st));
+    if (chunk_crc_out)
+        for (size_t b = 0; b < n; b++) {
+            const size_t nc = div_up(lens[b], chunk);
+            if (nc && chunk_crc_out[b]) CK(cudaMemcpyAsync(chunk_crc_out[b], d_crc + desc[b].first_chunk, 4 * nc, cudaMemcpyDeviceToHost, st));
+        }
+    CK(cudaStreamSynchronize(st));
+    return GPU_EC_OK;
 }
 
 // ---- batches: stripe i -> device i mod G, several slots (streams) per device in flight --------

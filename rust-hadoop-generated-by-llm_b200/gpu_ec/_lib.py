@@ -82,6 +82,7 @@ SIGNATURES = {
     "gpu_ec_crc32_chunks": (_i, [_vp, _sz, _sz, _i, _vp]),
     "gpu_ec_verify_chunks": (_i, [_vp, _sz, _sz, _i, _vp, _sz, _vp]),
     "gpu_ec_block_checksums": (_i, [_vp, _sz, _sz, _i, _vp, _vp]),
+    "gpu_ec_block_checksums_batch": (_i, [_sz, _vp, _vp, _sz, _i, _vp, _vp]),
     "gpu_ec_encode_batch": (_i, [_vp, _sz, _sz, _i, _i, _vp, _vp, _vp]),
     "gpu_ec_reconstruct_batch": (_i, [_vp, _vp, _sz, _sz, _i, _i]),
     "gpu_ec_verify_chunks_batch": (_i, [_sz, _vp, _vp, _sz, _i, _vp, _vp, _vp, _vp]),

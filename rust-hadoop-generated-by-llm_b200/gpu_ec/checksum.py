@@ -60,6 +60,20 @@ def block_checksums(data, chunk: int = CHECKSUM_CHUNK_SIZE, poly: int = POLY_IEE
     return whole.value, out
 
 
+def block_checksums_batch(blocks: Sequence, chunk: int = CHECKSUM_CHUNK_SIZE, poly: int = POLY_IEEE):
+    """block_checksums for many (small) blocks with one launch and one synchronisation: what a chunkserver does
+    per WriteBlock (chunkserver.rs:746-769 + :195), batched. -> (whole CRCs uint32[n], [chunk CRC arrays])."""
+    arrs = [_as_u8(b) for b in blocks]
+    n = len(arrs)
+    outs = [np.empty((a.size + chunk - 1) // chunk, dtype=np.uint32) for a in arrs]
+    whole = np.zeros(n, dtype=np.uint32)
+    dptr = (C.c_void_p * n)(*[a.ctypes.data if a.size else None for a in arrs])
+    optr = (C.c_void_p * n)(*[o.ctypes.data if o.size else None for o in outs])
+    lens = (C.c_size_t * n)(*[a.size for a in arrs])
+    check(lib().gpu_ec_block_checksums_batch(n, dptr, lens, chunk, poly, whole.ctypes.data if n else None, optr))
+    return whole, outs
+
+
 def verify_chunks(data, meta_be: bytes, chunk: int = CHECKSUM_CHUNK_SIZE, poly: int = POLY_IEEE) -> Optional[str]:
     """The compare of chunkserver.rs:265-289 -> None when OK, else the reference's error string."""
     d = _as_u8(data)

@@ -110,11 +110,10 @@ pub fn reconstruct_one(shards: &mut [Option<Vec<u8>>], k: usize, m: usize, shard
     let s = shards.iter().flatten().map(|v| v.len()).next().unwrap_or(0);
     let present: Vec<u8> = shards.iter().map(|o| o.is_some() as u8).collect();
     let mut target = vec![0u8; s];
-    let mut dummy = vec![0u8; 0];
     let ptrs: Vec<*mut u8> = shards.iter_mut().enumerate().map(|(i, o)| match o {
         Some(v) => v.as_mut_ptr(),
         None if i == shard_index => target.as_mut_ptr(),
-        None => dummy.as_mut_ptr(),
+        None => std::ptr::null_mut(), // absent and not wanted: gpu_ec_reconstruct_only neither reads nor writes it
     }).collect();
     let want = [shard_index as c_int];
     let rc = unsafe { ffi::gpu_ec_reconstruct_only(ptrs.as_ptr(), present.as_ptr(), s, k as c_int, m as c_int, want.as_ptr(), 1) };

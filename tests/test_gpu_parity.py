@@ -264,6 +264,33 @@ def test_block_checksums_one_pass(L, orc):
     assert whole == zlib.crc32(rnd(300_000, 5).tobytes()) and chunks.size == 5
 
 
+def test_block_checksums_batch_one_launch(L, orc):
+    """Many WriteBlocks at once (chunkserver.rs:746-769 + :195 each): same CRCs as block by block, as the oracle,
+    as zlib; ragged last chunks, empty blocks, and exactly one CRC launch + one fold launch for the whole batch."""
+    sizes = [0, 1, 61, 511, 512, 513, 4096, 65_536, 65_537, 1 << 20, 1_000_003, 0, 700, 131_072 + 17]
+    blocks = [rnd(n, 900 + i) for i, n in enumerate(sizes)]
+    before = L.gpu_ec_kernel_launch_count()
+    whole, chunks = checksum.block_checksums_batch(blocks)
+    assert L.gpu_ec_kernel_launch_count() - before == 2
+    for b, w, c in zip(blocks, whole, chunks):
+        assert int(w) == zlib.crc32(b.tobytes()), b.size
+        assert np.array_equal(c, orc.crc32_chunks(b)), b.size
+        w1, c1 = checksum.block_checksums(b)
+        assert w1 == int(w) and np.array_equal(c1, c)
+    # Castagnoli and another chunk size; a chunk size the one-launch layout does not serve falls back block by block
+    whole, chunks = checksum.block_checksums_batch(blocks, chunk=1024, poly=gpu_ec.POLY_CASTAGNOLI)
+    for b, w, c in zip(blocks, whole, chunks):
+        assert int(w) == orc.crc32(b, orc.POLY_CASTAGNOLI) and np.array_equal(c, orc.crc32_chunks(b, 1024, orc.POLY_CASTAGNOLI))
+    whole, chunks = checksum.block_checksums_batch(blocks[:6], chunk=4096)
+    for b, w, c in zip(blocks[:6], whole, chunks):
+        assert int(w) == zlib.crc32(b.tobytes()) and np.array_equal(c, orc.crc32_chunks(b, 4096))
+    assert checksum.block_checksums_batch([])[1] == []
+    big = [rnd((1 << 20) + 300 * i, 70 + i) for i in range(70)]  # > 64 MiB in total: copied block by block, not packed
+    whole, chunks = checksum.block_checksums_batch(big)
+    for b, w, c in zip(big[::23], whole[::23], chunks[::23]):
+        assert int(w) == zlib.crc32(b.tobytes()) and np.array_equal(c, orc.crc32_chunks(b))
+
+
 def test_verify_semantics(L, orc):
     blk = np.frombuffer(b"Hello, world! This is a test block for checksum verification.", dtype=np.uint8).copy()
     meta = checksum.meta_bytes(checksum.calculate_checksums(blk))

@@ -29,9 +29,14 @@ def main():
     rows = list(csv.reader(io.StringIO(raw)))
     H, U = rows[0], rows[1]
     lines = [f"# {rep} — extracted with `ncu -i ... --page raw --csv` (tools/ncu_summary.py)"]
+    seen = set()
     for r in rows[2:]:
         d = dict(zip(H, r))
         u = dict(zip(H, U))
+        key = (d.get("Kernel Name"), d.get("Grid Size"), d.get("Block Size"))
+        if key in seen:   # one entry per kernel and launch shape (repeat launches differ by a fraction of a percent)
+            continue
+        seen.add(key)
         lines.append("")
         lines.append(f"== {d.get('Kernel Name', '?')}  grid {d.get('Grid Size', '?')} block {d.get('Block Size', '?')}")
         for k in KEYS:
