@@ -308,6 +308,31 @@ __device__ __forceinline__ uint32_t packed_products_rot(const RsParams &p, int j
     return v;
 }
 
+// the same for either table layout (rs_lut8's classic [K][256][32] when K > 5)
+template <int K, bool FAST, int J, typename F>
+__device__ __forceinline__ void rs_accumulate_reload_any(uint4 (&d)[K], uint32_t (&acc)[16], uint32_t tl, uint32_t lane4, F &&reload) {
+    if constexpr (J < K) {
+        const uint32_t w[4] = {d[J].x, d[J].y, d[J].z, d[J].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if constexpr (FAST) {
+                acc[q * 4 + 0] ^= lut_fast<J, 0>(lane4, w[q]);
+                acc[q * 4 + 1] ^= lut_fast<J, 1>(lane4, w[q]);
+                acc[q * 4 + 2] ^= lut_fast<J, 2>(lane4, w[q]);
+                acc[q * 4 + 3] ^= lut_fast<J, 3>(lane4, w[q]);
+            } else {
+                const uint32_t tj = tl + J * (256 * 32 * 4);
+                acc[q * 4 + 0] ^= lut_lds<0>(tj, byte_of<0>(w[q]));
+                acc[q * 4 + 1] ^= lut_lds<0>(tj, byte_of<1>(w[q]));
+                acc[q * 4 + 2] ^= lut_lds<0>(tj, byte_of<2>(w[q]));
+                acc[q * 4 + 3] ^= lut_lds<0>(tj, w[q] >> 24);
+            }
+        }
+        reload(J);
+        rs_accumulate_reload_any<K, FAST, J + 1>(d, acc, tl, lane4, reload);
+    }
+}
+
 // lookups of input shard J, then `reload(J)`: d[J] is dead from here on, the next tile's vector may land in it
 template <int KH, int J, typename F>
 __device__ __forceinline__ void rs_accumulate_reload(uint4 (&d)[KH], uint32_t (&acc)[16], uint32_t lane4, F &&reload) {
@@ -573,6 +598,149 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         v = nv;
     }
     cluster_sync_all();  // neither CTA may retire while its partner can still write into it or signal it
+}
+
+// ---------------------------------------------------------------------------------------------
+// The single-SM form for n_in = K <= 7, n_out <= 4 (RS(6,3), RS(4,2), ...): rs_lut8_kernel's tables (one
+// lookup per input byte, all output rows in one packed word) with the same walk, register reload and
+// sparse-fold accumulators as above; no cluster, no exchange: a CTA loads all K data vectors of a column,
+// stores its n_out parity vectors and checksums all K + n_out of them in the same tile.
+template <int K, int NT>
+__global__ void __launch_bounds__(NT, 1) rs_lut8_crc_kernel(const __grid_constant__ FusedParams fp) {
+    extern __shared__ __align__(16) uint32_t rs_tab[];  // [K][256][32]
+    const RsParams &p = fp.rs;
+    const unsigned int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NW = NT / 32;
+    constexpr bool FAST = (K <= 5);
+    const uint32_t s0 = static_cast<uint32_t>(__cvta_generic_to_shared(rs_tab));
+    if (FAST && s0 > LUT_FRAG1) __trap();
+    for (int e0 = warp * 32; e0 < K * 256; e0 += NW * 32) {
+        const int e = e0 + lane;
+        const uint32_t v = packed_products(p, e >> 8, static_cast<uint32_t>(e & 255));
+#pragma unroll 8
+        for (int q = 0; q < 32; q++) {
+            const int eq = e0 + q;
+            const uint32_t addr = FAST ? lut_fast_addr(eq >> 8, static_cast<uint32_t>(eq & 255), lane) : s0 + (eq * 32 + lane) * 4;
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(__shfl_sync(0xffffffffu, v, q)) : "memory");
+        }
+    }
+    __syncthreads();
+    const uint32_t tl = s0 + lane * 4;
+    const uint32_t lane4 = lane * 4u;
+
+    const unsigned long long n_ctas = gridDim.x, cta = blockIdx.x;
+    const unsigned int dv = fp.g.dv, R = fp.g.rseg, ng = fp.g.ng, lead = fp.g.lead;
+    const unsigned int last_vec = p.nvec - 1;
+    const int n_out = p.n_out;
+    const unsigned long long my_jobs = cta < fp.n_jobs ? (fp.n_jobs - cta + n_ctas - 1) / n_ctas : 0ull;
+    const unsigned long long my_tiles = my_jobs * R;
+    const unsigned long long lp_stride = static_cast<unsigned long long>(ng) * fp.n_shards;
+
+    struct Job {
+        const uint8_t *stripe;
+        uint2 *lp;
+        unsigned int o, stripe_i;
+        bool col, lastcls;
+    };
+    auto setup_job = [&](unsigned long long job) -> Job {
+        Job J;
+        const unsigned long long st = job / fp.n_class;
+        const unsigned int cls = static_cast<unsigned int>(job - st * fp.n_class);
+        J.stripe_i = static_cast<unsigned int>(st);
+        J.o = cls * NT + threadIdx.x;
+        J.col = J.o < dv;
+        J.lastcls = (cls + 1 == fp.n_class);
+        J.stripe = p.base + st * p.stripe_stride;
+        J.lp = fp.qlog + ((st * R) * ng + (J.o >> 5)) * fp.n_shards;
+        return J;
+    };
+    uint4 A[K], AP[RS_MAX_OUT];
+#pragma unroll
+    for (int j = 0; j < K; j++) A[j] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int r = 0; r < RS_MAX_OUT; r++) AP[r] = make_uint4(0, 0, 0, 0);
+    auto crc_fast = [&](uint4 &acc, const uint4 &d, uint2 *lp) {
+        if (lane == 0) *lp = make_uint2(acc.x, acc.y);
+        sfold_mul(acc, fp.g.sh, lane);
+        xor4(acc, d);
+    };
+    auto crc_slow = [&](uint4 &acc, uint4 d, const Job &J, bool ok, unsigned int v, bool last, uint2 *lp, unsigned int slot) {
+        and4(d, ok ? 0xFFFFFFFFu : 0u);
+        if (v == last_vec) { d.x &= fp.tail_mask[0]; d.y &= fp.tail_mask[1]; d.z &= fp.tail_mask[2]; d.w &= fp.tail_mask[3]; }
+        if (lane == 0 && J.col) *lp = make_uint2(acc.x, acc.y);
+        sfold_mul(acc, fp.g.sh, lane);
+        xor4(acc, d);
+        if (last) {
+            if (J.col) fp.dump[(static_cast<unsigned long long>(J.stripe_i) * fp.n_shards + slot) * dv + J.o] = acc;
+            acc = make_uint4(0, 0, 0, 0);
+        }
+    };
+
+    uint4 cur[K];
+    Job J = setup_job(cta < fp.n_jobs ? cta : 0ull);
+    unsigned long long job = cta;
+    unsigned int s = 0;
+    bool ok = J.col && J.o >= lead;
+    unsigned int v = ok ? J.o - lead : 0u;
+    uint2 *lp = J.lp;
+    if (my_tiles) {
+#pragma unroll
+        for (int j = 0; j < K; j++) cur[j] = ld_vec(J.stripe + static_cast<unsigned long long>(v + p.in_off16[j]) * 16ull);
+    }
+    for (unsigned long long ti = 0; ti < my_tiles; ti++) {
+        const bool last = (s + 1 == R);
+        const bool slow = (s == 0) || J.lastcls || last;
+        if (!slow) {
+#pragma unroll
+            for (int j = 0; j < K; j++) crc_fast(A[j], cur[j], lp + j);  // data slot of input j is j (encode)
+        } else {
+#pragma unroll
+            for (int j = 0; j < K; j++) crc_slow(A[j], cur[j], J, ok, v, last, lp + j, static_cast<unsigned int>(j));
+        }
+        Job NJ = J;
+        bool nok = J.col;
+        unsigned int nv = (s + 1) * dv + J.o - lead;
+        if (last) {
+            NJ = setup_job(job + n_ctas < fp.n_jobs ? job + n_ctas : job);
+            nok = NJ.col && NJ.o >= lead;
+            nv = NJ.o - lead;
+        }
+        if (!nok) nv = 0u;
+        const bool more = ti + 1 < my_tiles;
+        const uint8_t *nsrc = NJ.stripe;
+
+        uint32_t acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) acc[i] = 0;
+        rs_accumulate_reload_any<K, FAST, 0>(cur, acc, tl, lane4, [&](int j) {
+            if (more) cur[j] = ld_vec(nsrc + static_cast<unsigned long long>(nv + p.in_off16[j]) * 16ull);
+        });
+        uint32_t o[4][4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
+        uint8_t *ws = const_cast<uint8_t *>(J.stripe);
+#pragma unroll
+        for (int r = 0; r < RS_MAX_OUT; r++) {
+            if (r < n_out) {
+                const uint4 pv = make_uint4(o[0][r], o[1][r], o[2][r], o[3][r]);
+                if (ok) *reinterpret_cast<uint4 *>(ws + static_cast<unsigned long long>(v + p.out_off16[r]) * 16ull) = pv;
+                uint2 *l2 = lp + p.out_idx[r];
+                if (!slow) crc_fast(AP[r], pv, l2);
+                else crc_slow(AP[r], pv, J, ok, v, last, l2, static_cast<unsigned int>(p.out_idx[r]));
+            }
+        }
+        if (last) {
+            J = NJ;
+            job += n_ctas;
+            s = 0;
+            lp = J.lp;
+        } else {
+            s++;
+            lp += lp_stride;
+        }
+        ok = nok;
+        v = nv;
+    }
 }
 
 }  // namespace gpu_ec

@@ -122,6 +122,13 @@ static int dev_prepare(Dev &d) {
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(4)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(5)));
     CK(cudaFuncSetAttribute(rs_lut8x2_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, x2_smem_bytes(6)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<1, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(1)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<2, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(2)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<3, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(3)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<4, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(4)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<5, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(5)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<6, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(6)));
+    CK(cudaFuncSetAttribute(rs_lut8_crc_kernel<7, FUSED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, lut8_smem_bytes(7)));
     CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
     CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<4, FUSED_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
     CK(cudaFuncSetAttribute(rs_x2_crc_fast_kernel<5, FUSED_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, LUT_FAST_RS_BYTES));
@@ -848,10 +855,11 @@ static int apply_x2_fast(Dev &d, const RsParams &rp, size_t n_stripes, cudaStrea
 // -> *done = false when the shape is not one the fused kernel serves (caller runs the two-pass path)
 static int encode_crc_fused(Dev &d, const gpu_ec_stripes &s, int k, int m, uint32_t *shard_crc, cudaStream_t st, bool *done) {
     *done = false;
-    if (k <= RS_LUT8_MAX_IN || k > 2 * RS_X2_MAX_KH || m > RS_MAX_OUT || !sfold_enabled()) return GPU_EC_OK;
+    if (k > 2 * RS_X2_MAX_KH || m > RS_MAX_OUT || !sfold_enabled()) return GPU_EC_OK;
+    const bool single = k <= RS_LUT8_MAX_IN;  // one CTA per SM holds all k tables: no cluster
     if (s.n_stripes == 0 || s.shard_len == 0 || s.n_stripes * static_cast<size_t>(k + m) >= (1ull << 32)) return GPU_EC_OK;
     const int n = k + m;
-    const int n_clusters_max = d.sm_count / 2;
+    const int n_clusters_max = single ? d.sm_count : d.sm_count / 2;  // CTAs (single) or 2-CTA clusters that run at once
     SfoldPlan pl;
     if (!sfold_plan(s.n_stripes, s.shard_len, FUSED_THREADS, static_cast<size_t>(n_clusters_max), false, pl)) return GPU_EC_OK;
     const unsigned long long n_jobs = static_cast<unsigned long long>(s.n_stripes) * pl.n_class;
@@ -886,9 +894,22 @@ static int encode_crc_fused(Dev &d, const gpu_ec_stripes &s, int k, int m, uint3
     fp.qlog = reinterpret_cast<uint2 *>(scratch + qlog_off);
     const int n_clusters = static_cast<int>(std::min<unsigned long long>(n_jobs, static_cast<unsigned long long>(n_clusters_max)));
     const int kh = (k + 1) / 2;
+    if (single) {
+        const size_t smem = lut8_smem_bytes(k);
+        switch (k) {
+            case 1: rs_lut8_crc_kernel<1, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            case 2: rs_lut8_crc_kernel<2, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            case 3: rs_lut8_crc_kernel<3, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            case 4: rs_lut8_crc_kernel<4, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            case 5: rs_lut8_crc_kernel<5, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            case 6: rs_lut8_crc_kernel<6, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+            default: rs_lut8_crc_kernel<7, FUSED_THREADS><<<n_clusters, FUSED_THREADS, smem, st>>>(fp); break;
+        }
+    }
     static const bool generic_only = getenv("GPU_EC_FUSED_GENERIC") != nullptr;  // kernel experiments only
     const bool fast = (k == 2 * kh) && m == RS_MAX_OUT && (kh == 4 || kh == 5) && !generic_only;
-    cudaError_t e = fast ? (kh == 4 ? launch_fused_fast<4, true>(fp, n_clusters, st) : launch_fused_fast<5, true>(fp, n_clusters, st))
+    cudaError_t e = single ? cudaGetLastError()
+                  : fast ? (kh == 4 ? launch_fused_fast<4, true>(fp, n_clusters, st) : launch_fused_fast<5, true>(fp, n_clusters, st))
                   : kh <= 4 ? launch_fused_x2<4>(fp, n_clusters, st) : kh == 5 ? launch_fused_x2<5>(fp, n_clusters, st) : launch_fused_x2<6>(fp, n_clusters, st);
     g_launches++;
     int rc = GPU_EC_OK;

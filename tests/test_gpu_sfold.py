@@ -70,7 +70,8 @@ def test_sfold_adversarial_fills(L):
 # ---------------------------------------------------------------- fused encode + shard CRCs (fused_kernels.cuh)
 FUSED = [(10, 4, (8 << 20) + 5, 20), (10, 4, 64 << 20, 3), (8, 3, (4 << 20) + 1, 40), (12, 4, (6 << 20) - 7, 24),
          (10, 2, (8 << 20) + 16, 16), (9, 4, 5_000_011, 33), (11, 1, 9_999_999, 17), (8, 4, (4 << 20) + 33, 30),
-         (10, 4, 3_000_000, 75)]
+         (10, 4, 3_000_000, 75), (6, 3, (64 << 20) + 1, 6), (6, 3, 4_000_000, 160), (4, 2, 2_000_003, 200), (7, 4, 8_000_000, 40),
+         (2, 2, 1_500_000, 300), (5, 1, 3_333_333, 150), (1, 1, 1_000_000, 400), (3, 3, (8 << 20) + 9, 50)]
 
 
 @pytest.mark.parametrize("k,m,stripe_len,n_stripes", FUSED)

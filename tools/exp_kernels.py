@@ -87,6 +87,21 @@ def fused(n=256):
     print(f"rs(10,4) encode only: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
 
 
+def fused63(n=64):
+    """RS(6,3) encode + 9 shard CRCs + CRC(original) on 64 MiB blocks: single pass vs two-pass vs encode only"""
+    S = gpu_ec.erasure.shard_len(64 << 20, 6)
+    b = device.StripeBatch(n, 6, 3, S)
+    b.fill_synthetic(4, original_len=64 << 20)
+    a = 9 * S * n
+    for mode, name in (("1", "fused"), ("0", "two-pass")):
+        os.environ["GPU_EC_SFOLD"] = mode
+        l0 = L.gpu_ec_kernel_launch_count()
+        ms = timed(lambda: b.encode_crc(original_len=64 << 20), 10)
+        print(f"rs(6,3)+9crc n={n} {name}: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f} launches/step={(L.gpu_ec_kernel_launch_count()-l0)//13}")
+    ms = timed(b.encode, 10)
+    print(f"rs(6,3) encode only: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
+
+
 def rs(k, m, stripe_len, n):
     S = gpu_ec.erasure.shard_len(stripe_len, k)
     b = device.StripeBatch(n, k, m, S)
@@ -114,6 +129,8 @@ if __name__ == "__main__":
         crc()
     elif what == "sfold":
         sfold()
+    elif what == "fused63":
+        fused63(int(sys.argv[2]) if len(sys.argv) > 2 else 64)
     elif what == "fused":
         fused(int(sys.argv[2]) if len(sys.argv) > 2 else 256)
     elif what == "rs104":
