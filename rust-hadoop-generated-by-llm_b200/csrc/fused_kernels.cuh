@@ -333,6 +333,43 @@ __device__ __forceinline__ void rs_accumulate_reload_any(uint4 (&d)[K], uint32_t
     }
 }
 
+// one table word of shard J (compile time), byte I of w, either layout
+template <int J, int I, bool FAST>
+__device__ __forceinline__ uint32_t rs_lut_word(uint32_t tl, uint32_t lane4, uint32_t w) {
+    if constexpr (FAST) return lut_fast<J, I>(lane4, w);
+    else return lut_lds<0>(tl + J * (256 * 32 * 4), I == 3 ? (w >> 24) : byte_of<I>(w));
+}
+// all lookups of a tile, XORs merged three table words at a time (one LOP3 each): shards J, J+1, J+2 per step;
+// FIRST starts the accumulators instead of adding to them. `reload(j)` is called once shard j's registers are dead.
+template <int K, bool FAST, int J, typename F>
+__device__ __forceinline__ void rs_lookup_merged3(uint4 (&d)[K], uint32_t (&acc)[16], uint32_t tl, uint32_t lane4, F &&reload) {
+    if constexpr (J < K) {
+        constexpr int N = (K - J >= 3) ? 3 : (K - J);
+        const uint32_t a[4] = {d[J].x, d[J].y, d[J].z, d[J].w};
+        const uint32_t b[4] = {d[J + (N > 1 ? 1 : 0)].x, d[J + (N > 1 ? 1 : 0)].y, d[J + (N > 1 ? 1 : 0)].z, d[J + (N > 1 ? 1 : 0)].w};
+        const uint32_t c[4] = {d[J + (N > 2 ? 2 : 0)].x, d[J + (N > 2 ? 2 : 0)].y, d[J + (N > 2 ? 2 : 0)].z, d[J + (N > 2 ? 2 : 0)].w};
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            uint32_t t0 = rs_lut_word<J, 0, FAST>(tl, lane4, a[q]), t1 = rs_lut_word<J, 1, FAST>(tl, lane4, a[q]);
+            uint32_t t2 = rs_lut_word<J, 2, FAST>(tl, lane4, a[q]), t3 = rs_lut_word<J, 3, FAST>(tl, lane4, a[q]);
+            if constexpr (N > 1) {
+                t0 ^= rs_lut_word<J + 1, 0, FAST>(tl, lane4, b[q]); t1 ^= rs_lut_word<J + 1, 1, FAST>(tl, lane4, b[q]);
+                t2 ^= rs_lut_word<J + 1, 2, FAST>(tl, lane4, b[q]); t3 ^= rs_lut_word<J + 1, 3, FAST>(tl, lane4, b[q]);
+            }
+            if constexpr (N > 2) {
+                t0 ^= rs_lut_word<J + 2, 0, FAST>(tl, lane4, c[q]); t1 ^= rs_lut_word<J + 2, 1, FAST>(tl, lane4, c[q]);
+                t2 ^= rs_lut_word<J + 2, 2, FAST>(tl, lane4, c[q]); t3 ^= rs_lut_word<J + 2, 3, FAST>(tl, lane4, c[q]);
+            }
+            if constexpr (J == 0) { acc[q * 4 + 0] = t0; acc[q * 4 + 1] = t1; acc[q * 4 + 2] = t2; acc[q * 4 + 3] = t3; }
+            else { acc[q * 4 + 0] ^= t0; acc[q * 4 + 1] ^= t1; acc[q * 4 + 2] ^= t2; acc[q * 4 + 3] ^= t3; }
+        }
+        reload(J);
+        if constexpr (N > 1) reload(J + 1);
+        if constexpr (N > 2) reload(J + 2);
+        rs_lookup_merged3<K, FAST, J + 3>(d, acc, tl, lane4, reload);
+    }
+}
+
 // lookups of input shard J, then `reload(J)`: d[J] is dead from here on, the next tile's vector may land in it
 template <int KH, int J, typename F>
 __device__ __forceinline__ void rs_accumulate_reload(uint4 (&d)[KH], uint32_t (&acc)[16], uint32_t lane4, F &&reload) {
@@ -557,6 +594,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         const bool more = ti + 1 < my_tiles;
         const uint8_t *nsrc = NJ.stripe;
 
+        if constexpr (!CRC) {
+            // without the checksum work the kernel waits on memory (ncu: long_scoreboard 2.1 per issue): pull the tile
+            // after next into L2 now, so the register reload below finds it a quarter of the DRAM latency away
+            if (s + 2 < R && J.col) {
+                const unsigned int pv = nv + dv;
+#pragma unroll
+                for (int j = 0; j < KH; j++)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(J.stripe + static_cast<unsigned long long>(pv + my_in_off[j]) * 16ull));
+            }
+        }
         // ---- lookups; each shard's registers are refilled with the next tile as soon as they are dead
         uint32_t acc[16];
         rs_lookup_merged<KH>(cur, acc, lane4, [&](int j) {
@@ -710,9 +757,7 @@ __global__ void __launch_bounds__(NT, 1) rs_lut8_crc_kernel(const __grid_constan
         const uint8_t *nsrc = NJ.stripe;
 
         uint32_t acc[16];
-#pragma unroll
-        for (int i = 0; i < 16; i++) acc[i] = 0;
-        rs_accumulate_reload_any<K, FAST, 0>(cur, acc, tl, lane4, [&](int j) {
+        rs_lookup_merged3<K, FAST, 0>(cur, acc, tl, lane4, [&](int j) {
             if (more) cur[j] = ld_vec(nsrc + static_cast<unsigned long long>(nv + p.in_off16[j]) * 16ull);
         });
         uint32_t o[4][4];

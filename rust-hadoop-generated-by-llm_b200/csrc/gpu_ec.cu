@@ -649,7 +649,7 @@ static int launch_sfold_finish(Dev &d, const SfoldPlan &pl, size_t n_buf, size_t
     f.x_seg = x8n_modp(16ull * pl.g.dv * pl.g.rseg, P);
     f.x_inv_pad = xinv8n_modp(pl.nvec * 16 - len, P);
     f.cz_len = crc_of_zeros(len, P);
-    const int grid = static_cast<int>(std::min<size_t>(n_buf, static_cast<size_t>(d.sm_count) * 4));
+    const int grid = static_cast<int>(std::min<size_t>(n_buf, static_cast<size_t>(d.sm_count) * 8));  // latency-bound: fill the SMs with warps
     crc_sfold_finish_kernel<<<grid, 256, 0, st>>>(f);
     g_launches++;
     CK(cudaGetLastError());

@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(256) crc_sfold_finish_kernel(const __grid_cons
                 uint32_t T = 0;
                 if (slot >= off) {
                     const unsigned int g = slot - off;
-#pragma unroll 4
+#pragma unroll 8
                     for (unsigned int s = (seg ? 0u : p.g.skip_rows) + 1; s < rseg; s++) {
                         const uint2 w = __ldg(ql + s * qs_s + g * qs_g);
                         // bits that left the group at step s: virtual words -1 (hm1) and -2 (hm2) in front of it
