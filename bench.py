@@ -159,6 +159,10 @@ def cpu_others(oracle, np):
     out["rs104_encode_plus_14_crc_64MiB_stripes"] = {"cpu_port_GBps": round(14 * S4 * n4 / tN / 1e9, 2), "cpu_port_1thread_GBps": round(14 * S4 / t1 / 1e9, 3),
                                                      "cpu_cores": threads, "cpu_sample": f"{n4} of the 1024 stripes, 3 passes (best)"}
     out["rs104_encode_only"] = {"cpu_port_GBps": round(14 * S4 * n4 / tNe / 1e9, 2), "cpu_cores": threads}
+    S6 = oracle.shard_len(STRIPE_LEN, K_DATA)
+    tN = min(oracle.bench_encode(d, STRIPE_LEN, n4, K_DATA, M_PAR, threads, True) for _ in range(3))
+    out["rs63_encode_plus_9_crc_64MiB_blocks"] = {"cpu_port_GBps": round(9 * S6 * n4 / tN / 1e9, 2), "cpu_cores": threads,
+                                                  "cpu_sample": f"{n4} of the 64 blocks, 3 passes (best)"}
     # config 2: CRC-32 IEEE per 512 B and per 64 KiB: PCLMULQDQ port (what crc32fast runs on this CPU) and zlib
     samp = d[:256 << 20]
     for chunk in (512, 65536):
@@ -428,7 +432,7 @@ def main():
     n_local = args.stripes  # weak scaling: every rank owns `stripes` stripes of the global round-robin
     batch = device.StripeBatch(n_local, K_DATA, M_PAR, S)
     # global stripe id of local stripe i is i*world + rank; seeds differ per rank so ranks hold different bytes
-    batch.fill_synthetic(SEED + rank)
+    batch.fill_synthetic(SEED + rank, original_len=STRIPE_LEN)
     torch.cuda.synchronize()
 
     # ---- parity gate: no number is reported unless the bytes match the oracle
@@ -460,6 +464,18 @@ def main():
     # ---- secondary configs (device-resident), each with its own roofline fraction
     sub = {}
     if not args.no_sub:
+        # the headline code with its checksums (client/src/mod.rs:600-611 at RS(6,3)): parity + 9 shard CRCs + CRC(original), one pass
+        import zlib
+        crc63, full63 = batch.encode_crc(original_len=STRIPE_LEN)
+        torch.cuda.synchronize()
+        d0 = np.concatenate([batch.shard_host(0, j) for j in range(K_DATA)])
+        w0 = oracle.encode(d0[:STRIPE_LEN], K_DATA, M_PAR)
+        if device.u32(crc63)[0].tolist() != [zlib.crc32(x.tobytes()) for x in w0] or int(device.u32(full63)[0]) != zlib.crc32(d0[:STRIPE_LEN].tobytes()):
+            raise SystemExit("PARITY FAILURE fused RS(6,3)+CRC")
+        ms63, l63 = timed(lambda: batch.encode_crc(original_len=STRIPE_LEN), 10, 3)
+        sub["rs63_encode_plus_9_crc_64MiB_blocks"] = {"GBps_algorithmic": round(alg_bytes_rank * world / ms63 / 1e6, 1), "ms": round(ms63, 3),
+                                                      "roofline_frac": round(alg_bytes_rank / ms63 / 1e6 / peak, 4), "launches_per_step": int(l63) // 10,
+                                                      "note": "one pass over HBM: single-CTA byte-LUT encode with the 9 shard CRCs accumulated in registers, then the finisher"}
         del batch
         torch.cuda.empty_cache()
         # config 3: 4096 stripes of 1 MiB, RS(6,3), shards {1,4,7} erased -> one pass, reads k writes e
@@ -594,6 +610,7 @@ def main():
                 w = f"crc32_ieee_{chunk}B_chunks_1GiB"
                 other(w, "crc_segments_kernel (write)", "write_GBps", "roofline_frac_write", (1 << 30) + 4 * ((1 << 30) // chunk))
                 other(w, "crc_segments_kernel (verify)", "verify_GBps", "roofline_frac_verify", (1 << 30) + 4 * ((1 << 30) // chunk))
+            other("rs63_encode_plus_9_crc_64MiB_blocks", "rs_lut8_crc_kernel<6,384> + finisher", alg=alg_bytes_rank)
             other("rs104_encode_only", "rs_x2_crc_fast_kernel<5,384,false>", alg=a4)
             other("rs104_encode_plus_14_crc_64MiB_stripes", "rs_x2_crc_fast_kernel<5,384,true> + finisher", alg=a4)
         line = {

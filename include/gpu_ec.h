@@ -48,6 +48,8 @@ enum { GPU_EC_POLY_IEEE = 0, GPU_EC_POLY_CASTAGNOLI = 1 };
 
 /* ---- lifecycle ------------------------------------------------------------------------- */
 int gpu_ec_init(void);                       /* optional; every entry point initialises lazily */
+/* Frees streams and staging buffers. Call it only when no other thread is inside an entry point and none will
+ * enter one concurrently (a call racing a shutdown is undefined); the next call after it initialises again. */
 void gpu_ec_shutdown(void);
 int gpu_ec_device_count(void);               /* CUDA devices visible (0 if none) */
 /* Restrict host-pointer entry points to these CUDA ordinals (round-robin between them).

@@ -34,6 +34,7 @@ struct FusedParams {
     unsigned int n_shards;       // k + m: stream index = stripe * n_shards + slot
     unsigned long long n_jobs;   // n_stripes * n_class
     uint32_t tail_mask[4];       // keeps the bytes of a shard's last vector that lie inside shard_len
+    int prefetch;                // plain apply only: L2-prefetch the tile after next (helps short bursts, hurts sustained runs)
     uint4 *dump;                 // [n_stripes * n_shards][dv]
     uint2 *qlog;                 // [n_stripes][rseg][ng][n_shards]: lane 0 of a warp logs its streams side by side
 };
@@ -595,9 +596,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         const uint8_t *nsrc = NJ.stripe;
 
         if constexpr (!CRC) {
-            // without the checksum work the kernel waits on memory (ncu: long_scoreboard 2.1 per issue): pull the tile
-            // after next into L2 now, so the register reload below finds it a quarter of the DRAM latency away
-            if (s + 2 < R && J.col) {
+            // without the checksum work the kernel waits on memory in short runs at full clock (ncu: long_scoreboard
+            // 2.1 per issue): pulling the tile after next into L2 gave +6 % there (0.80 -> 0.85) but -12 % in long
+            // runs under the power cap (0.77 -> 0.67, 1 024 stripes), so it is off unless the caller's plan asks
+            if (fp.prefetch && s + 2 < R && J.col) {
                 const unsigned int pv = nv + dv;
 #pragma unroll
                 for (int j = 0; j < KH; j++)

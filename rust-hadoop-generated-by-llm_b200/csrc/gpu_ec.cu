@@ -844,6 +844,8 @@ static int apply_x2_fast(Dev &d, const RsParams &rp, size_t n_stripes, cudaStrea
     fp.n_class = static_cast<unsigned int>(n_class);
     fp.n_shards = 1;
     fp.n_jobs = n_stripes * n_class;
+    static const bool prefetch = getenv("GPU_EC_X2_PREFETCH") != nullptr;  // kernel experiments only (see fused_kernels.cuh)
+    fp.prefetch = prefetch ? 1 : 0;
     const int n_clusters = static_cast<int>(std::min<unsigned long long>(fp.n_jobs, n_clusters_max));
     const int kh = rp.n_in / 2;
     cudaError_t e = kh == 4 ? launch_fused_fast<4, false>(fp, n_clusters, st) : launch_fused_fast<5, false>(fp, n_clusters, st);

@@ -42,6 +42,13 @@ __device__ __forceinline__ uint32_t lut_fast(uint32_t lane4, uint32_t w) {
     uint32_t v;
     if constexpr (J < 4) {
         const uint32_t lb = ((J < 2) ? LUT_BLK_A : LUT_BLK_B) | lane4;
+#ifdef GPU_EC_LUT_BYTE3_FMA
+        if constexpr (I == 3) {
+            // top byte on the fma pipe (idle next to a saturated alu pipe): w >> 24 = umulhi(w, 2^8), then * 256 + base
+            asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(__umulhi(w, 256u) * 256u + lb), "n"((J & 1) ? 128 : 0));
+            return v;
+        }
+#endif
         asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(__byte_perm(w, lb, 0x7604 | (I << 4))), "n"((J & 1) ? 128 : 0));
     } else {
         const uint32_t base = ((J == 4) ? LUT_FRAG1 : LUT_FRAG2) + lane4;

@@ -134,7 +134,7 @@ if __name__ == "__main__":
     elif what == "fused":
         fused(int(sys.argv[2]) if len(sys.argv) > 2 else 256)
     elif what == "rs104":
-        rs(10, 4, 64 << 20, 48)
+        rs(10, 4, 64 << 20, int(sys.argv[2]) if len(sys.argv) > 2 else 48)
     elif what == "rs63":
         rs(6, 3, 64 << 20, 64)
 
