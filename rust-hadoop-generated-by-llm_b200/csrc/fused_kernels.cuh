@@ -547,11 +547,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         const unsigned int ps = tit & 1u, pu = tit >> 1;
         mbar_wait(my_full + ps * (NW * 8), pu & 1u);
         const uint4 *x = xbuf + ps * (2 * NT) + threadIdx.x;
-        uint4 o0 = x[0], o1 = x[NT];
-        xor4(o0, keep0);
-        xor4(o1, keep1);
+        uint4 p0 = x[0], p1 = x[NT];
+        xor4(p0, keep0);
+        xor4(p1, keep1);
         __syncwarp();
         if (lane == 0) mbar_arrive_peer(peer_empty + ps * (NW * 8));
+        // pairs (lo = positions 4q, 4q+1; hi = 4q+2, 4q+3) -> the two finished parity rows
+        const uint4 o0 = make_uint4(__byte_perm(p0.x, p0.y, 0x6420), __byte_perm(p0.z, p0.w, 0x6420), __byte_perm(p1.x, p1.y, 0x6420), __byte_perm(p1.z, p1.w, 0x6420));
+        const uint4 o1 = make_uint4(__byte_perm(p0.x, p0.y, 0x7531), __byte_perm(p0.z, p0.w, 0x7531), __byte_perm(p1.x, p1.y, 0x7531), __byte_perm(p1.z, p1.w, 0x7531));
         if (kok) {
             uint8_t *ws = const_cast<uint8_t *>(JJ.stripe);
             *reinterpret_cast<uint4 *>(ws + static_cast<unsigned long long>(kv + own_off0) * 16ull) = o0;
@@ -611,19 +614,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) rs_x2_crc_fas
         rs_lookup_merged<KH>(cur, acc, lane4, [&](int j) {
             if (more) cur[j] = ld_vec(nsrc + static_cast<unsigned long long>(nv + my_in_off[j]) * 16ull);
         });
-        uint32_t o[4][4];  // o[q][plane]
+        // ---- planes 0,1 go to the partner, planes 2,3 stay. No full 4x4 byte transposes: both halves travel as
+        // byte pairs (word = [pos a: plane A, plane B | pos a+1: plane A, plane B]), the receiver XORs like with like
+        // and only then separates the two rows: 16 + 8 PRMT per tile instead of 32.
+        uint32_t snd[8], kp[8];
 #pragma unroll
-        for (int q = 0; q < 4; q++) transpose4x4(&acc[q * 4], o[q]);
-
-        // ---- planes 0,1 go to the partner, planes 2,3 stay
+        for (int i = 0; i < 8; i++) {
+            snd[i] = __byte_perm(acc[2 * i], acc[2 * i + 1], 0x5410);
+            kp[i] = __byte_perm(acc[2 * i], acc[2 * i + 1], 0x7632);
+        }
         const unsigned int st_ = it & 1u, use_ = it >> 1;
         if (lane == 0) mbar_expect_tx(my_full + st_ * (NW * 8), 2u * 32u * 16u);
         mbar_wait(my_empty + st_ * (NW * 8), (use_ & 1u) ^ 1u);
         const uint32_t dst = xbuf_peer + (st_ * (2 * NT) + threadIdx.x) * 16u;
         const uint32_t sig = peer_full + st_ * (NW * 8);
-        st_async_peer(dst, make_uint4(o[0][0], o[1][0], o[2][0], o[3][0]), sig);
-        st_async_peer(dst + NT * 16, make_uint4(o[0][1], o[1][1], o[2][1], o[3][1]), sig);
-        const uint4 own_a = make_uint4(o[0][2], o[1][2], o[2][2], o[3][2]), own_b = make_uint4(o[0][3], o[1][3], o[2][3], o[3][3]);
+        st_async_peer(dst, make_uint4(snd[0], snd[1], snd[2], snd[3]), sig);
+        st_async_peer(dst + NT * 16, make_uint4(snd[4], snd[5], snd[6], snd[7]), sig);
+        const uint4 own_a = make_uint4(kp[0], kp[1], kp[2], kp[3]), own_b = make_uint4(kp[4], kp[5], kp[6], kp[7]);
 
         // ---- the previous tile of this job (sent a whole tile of work ago), then bookkeeping
         if (have_prev) finish(it - 1, J, s - 1, false, keep_ok, keep_v, lp - lp_stride);
