@@ -60,3 +60,43 @@ def test_crc_any_length_and_chunk(orc, n, chunk, seed, poly):
         assert checksum.verify_chunks(d, bytes(meta), chunk) == f"Checksum mismatch at chunk {i}"
         whole, chunks = checksum.block_checksums(d, chunk)
         assert whole == zlib.crc32(d.tobytes()) and np.array_equal(chunks, want)
+
+
+@st.composite
+def fused_case(draw):
+    k = draw(st.integers(1, 12))
+    m = draw(st.integers(1, 4))
+    # shards long enough for a sparse-fold stride (>= ~9 906 vectors) and enough stripes to fill the GPU
+    S = draw(st.integers(160_000, 700_000))
+    pad = draw(st.integers(0, k - 1))
+    n_stripes = draw(st.integers(30, 48))
+    seed = draw(st.integers(0, 2**31 - 1))
+    return k, m, S * k - pad, n_stripes, seed
+
+
+@settings(max_examples=10, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
+@given(fused_case())
+def test_fused_encode_crc_any_code(orc, case):
+    """gpu_ec_encode_crc_dev, single-pass path, random (k, m, length): parity + every shard CRC + CRC(original) of the
+    first and last stripe against the oracle / zlib, and all stripes against the two-pass path."""
+    import os
+    import torch
+    from gpu_ec import device
+    k, m, stripe_len, n_stripes, seed = case
+    S = erasure.shard_len(stripe_len, k)
+    b = device.StripeBatch(n_stripes, k, m, S)
+    b.fill_synthetic(seed, original_len=stripe_len)
+    os.environ["GPU_EC_SFOLD"] = "0"
+    crc_ref, full_ref = b.encode_crc(original_len=stripe_len)
+    torch.cuda.synchronize()
+    os.environ.pop("GPU_EC_SFOLD", None)
+    crc, full = b.encode_crc(original_len=stripe_len)
+    torch.cuda.synchronize()
+    assert np.array_equal(device.u32(crc), device.u32(crc_ref)), case
+    assert np.array_equal(device.u32(full), device.u32(full_ref)), case
+    for i in (0, n_stripes - 1):
+        data = np.concatenate([b.shard_host(i, j) for j in range(k)])[:stripe_len]
+        want = orc.encode(data, k, m)
+        assert all(np.array_equal(b.shard_host(i, s), want[s]) for s in range(k, k + m)), case
+        assert device.u32(crc)[i].tolist() == [zlib.crc32(x.tobytes()) for x in want], case
+        assert int(device.u32(full)[i]) == zlib.crc32(data.tobytes()), case

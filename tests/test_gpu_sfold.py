@@ -127,3 +127,42 @@ def test_host_encode_with_checksums_all_paths(L, k, m, n):
         if with_meta:
             for i in (0, k - 1, k, k + m - 1):
                 assert metas[i].tobytes() == orc.meta_encode_be(orc.crc32_chunks(want[i]))
+
+
+def test_fused_with_gaps_between_stripes_and_shards(L):
+    """gpu_ec_stripes with a shard_stride larger than the pitch and a stripe_stride larger than (k+m) shards:
+    the fused pass must address through the strides it is given, not assume a packed batch."""
+    import ctypes as C
+    import torch
+    from gpu_ec import device, erasure
+    from gpu_ec._lib import Stripes
+    from oracle import oracle as orc
+    k, m, stripe_len, n = 10, 4, (4 << 20) + 7, 40
+    S = erasure.shard_len(stripe_len, k)
+    shard_stride = (S + 255) // 256 * 256 + 512
+    stripe_stride = (k + m + 1) * shard_stride + 4096
+    buf = torch.empty(n * stripe_stride, dtype=torch.uint8, device="cuda")
+    device.fill_synthetic(buf, 0xEC0000C7)
+    view = buf.view(n, stripe_stride)
+    pad = S * k - stripe_len
+    if pad:
+        view[:, (k - 1) * shard_stride + S - pad:(k - 1) * shard_stride + S] = 0
+    d = Stripes(buf.data_ptr(), shard_stride, stripe_stride, S, n)
+    out = {}
+    for mode in ("0", "1"):
+        os.environ["GPU_EC_SFOLD"] = mode
+        crc = torch.zeros((n, k + m), dtype=torch.int32, device="cuda")
+        full = torch.zeros(n, dtype=torch.int32, device="cuda")
+        _lib.check(L.gpu_ec_encode_crc_dev(C.byref(d), k, m, stripe_len, 0, crc.data_ptr(), full.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        out[mode] = (device.u32(crc).copy(), device.u32(full).copy())
+    os.environ.pop("GPU_EC_SFOLD", None)
+    assert np.array_equal(out["0"][0], out["1"][0]) and np.array_equal(out["0"][1], out["1"][1])
+    i = n - 1
+    host = view[i].cpu().numpy()
+    data = np.concatenate([host[j * shard_stride:j * shard_stride + S] for j in range(k)])[:stripe_len]
+    want = orc.encode(data, k, m)
+    for s in range(k, k + m):
+        assert np.array_equal(host[s * shard_stride:s * shard_stride + S], want[s]), s
+    assert out["1"][0][i].tolist() == [zlib.crc32(x.tobytes()) for x in want]
+    assert int(out["1"][1][i]) == zlib.crc32(data.tobytes())
