@@ -71,6 +71,8 @@ struct Slot {
     size_t cap = 0;
     uint8_t *hbuf = nullptr;   // pinned host staging (batched small blocks: one H2D / one D2H per batch)
     size_t hcap = 0;
+    cudaStream_t stream2 = nullptr;   // second stream + events: D2H of a large single call overlaps its own H2D
+    cudaEvent_t ev[8] = {};
     bool busy = false;
 };
 struct Dev {
@@ -197,12 +199,16 @@ static int dev_of_ptr(const void *p, Dev **out) {
 struct Lease {
     Dev *d = nullptr;
     Slot *s = nullptr;
+    bool alone = false;  // no other caller held a slot of this device when this one was leased
     ~Lease() { release(); }
     void release() {
         if (d && s) {
             // every success path has already synchronised; on an early error return this drains copies that
             // may still target caller memory before the slot (and its staging buffer) is handed on
-            if (cudaSetDevice(d->ordinal) == cudaSuccess) cudaStreamSynchronize(s->stream);
+            if (cudaSetDevice(d->ordinal) == cudaSuccess) {
+                cudaStreamSynchronize(s->stream);
+                if (s->stream2) cudaStreamSynchronize(s->stream2);
+            }
             std::lock_guard<std::mutex> lk(d->mu);
             s->busy = false;
             d->cv.notify_all();
@@ -221,8 +227,19 @@ static int lease_on(Dev &d, Lease &l) {
         });
         s->busy = true;
         l.d = &d; l.s = s;
+        int busy = 0;
+        for (auto &x : d.slots) busy += x.busy ? 1 : 0;
+        l.alone = (busy == 1);
     }
     CK(cudaSetDevice(d.ordinal));
+    return GPU_EC_OK;
+}
+
+// second stream and events of a slot, created on first use (device current)
+static int slot_overlap_init(Slot &s) {
+    if (s.stream2) return GPU_EC_OK;
+    CK(cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking));
+    for (auto &e : s.ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     return GPU_EC_OK;
 }
 
@@ -1004,6 +1021,10 @@ void gpu_ec_shutdown(void) {
         cudaSetDevice(d.ordinal);
         for (auto &s : d.slots) {
             if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); s.stream = nullptr; }
+            if (s.stream2) {
+                cudaStreamSynchronize(s.stream2); cudaStreamDestroy(s.stream2); s.stream2 = nullptr;
+                for (auto &e : s.ev) if (e) { cudaEventDestroy(e); e = nullptr; }
+            }
             if (s.dbuf) { cudaFree(s.dbuf); s.dbuf = nullptr; s.cap = 0; }
             if (s.hbuf) { cudaFreeHost(s.hbuf); s.hbuf = nullptr; s.hcap = 0; }
         }
@@ -1281,18 +1302,47 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
     uint8_t *db = L.s->dbuf;
     // H2D: the contiguous input becomes k pitched rows; the tail of the last rows is zero padding
     const size_t full_rows = len / S, rem = len - full_rows * S;
-    if (full_rows) CK(cudaMemcpy2DAsync(db, pitch, data, S, S, full_rows, cudaMemcpyHostToDevice, st));
-    if (rem) CK(cudaMemcpyAsync(db + full_rows * pitch, data + full_rows * S, rem, cudaMemcpyHostToDevice, st));
-    for (size_t r = full_rows; r < static_cast<size_t>(k); r++) {
-        const size_t o = (r == full_rows) ? rem : 0;
-        CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
-    }
     gpu_ec_stripes sv{db, pitch, static_cast<size_t>(n) * pitch, S, 1};
     const bool want_crc = shard_crc_out || full_crc_out;
     uint32_t *d_crc = reinterpret_cast<uint32_t *>(db + crc_off);
     bool fused = false;  // one pass for parity + shard CRCs where the fused kernel serves the shape
-    if (want_crc && !meta_out) RET(encode_crc_fused(*L.d, sv, k, m, d_crc, st, &fused));
-    if (!fused) RET(encode_dev_impl(*L.d, sv, k, m, st));
+    // A large call that has the device to itself is latency-bound by its own copies (256 MiB: 4.8 ms in, 2.4 ms out,
+    // 0.1 ms of kernels): walk the stripe in column chunks so the parity of chunk c goes home on a second stream
+    // while chunk c+1 comes in. With other callers on the device the slots already overlap each other.
+    static const bool no_chunks = getenv("GPU_EC_NO_CHUNKED_COPY") != nullptr;  // experiments only
+    const bool chunked = L.alone && len >= (64u << 20) && !no_chunks;
+    bool parity_home = false;
+    if (chunked) {
+        RET(slot_overlap_init(*L.s));
+        cudaStream_t st2 = L.s->stream2;
+        for (size_t r = full_rows; r < static_cast<size_t>(k); r++) {
+            const size_t o = (r == full_rows) ? rem : 0;
+            CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
+        }
+        const size_t width = round_up(div_up(S, 8), 4096);
+        int c = 0;
+        for (size_t c0 = 0; c0 < S; c0 += width, c++) {
+            const size_t w = std::min(width, S - c0);
+            if (full_rows) CK(cudaMemcpy2DAsync(db + c0, pitch, data + c0, S, w, full_rows, cudaMemcpyHostToDevice, st));
+            if (rem > c0) CK(cudaMemcpyAsync(db + full_rows * pitch + c0, data + full_rows * S + c0, std::min(w, rem - c0), cudaMemcpyHostToDevice, st));
+            gpu_ec_stripes blk{db + c0, pitch, static_cast<size_t>(n) * pitch, w, 1};
+            RET(encode_dev_impl(*L.d, blk, k, m, st));
+            CK(cudaEventRecord(L.s->ev[c], st));
+            CK(cudaStreamWaitEvent(st2, L.s->ev[c], 0));
+            for (int r = 0; r < m; r++)
+                CK(cudaMemcpyAsync(shards_out[k + r] + c0, db + static_cast<size_t>(k + r) * pitch + c0, w, cudaMemcpyDeviceToHost, st2));
+        }
+        parity_home = true;
+    } else {
+        if (full_rows) CK(cudaMemcpy2DAsync(db, pitch, data, S, S, full_rows, cudaMemcpyHostToDevice, st));
+        if (rem) CK(cudaMemcpyAsync(db + full_rows * pitch, data + full_rows * S, rem, cudaMemcpyHostToDevice, st));
+        for (size_t r = full_rows; r < static_cast<size_t>(k); r++) {
+            const size_t o = (r == full_rows) ? rem : 0;
+            CK(cudaMemsetAsync(db + r * pitch + o, 0, S - o, st));
+        }
+        if (want_crc && !meta_out) RET(encode_crc_fused(*L.d, sv, k, m, d_crc, st, &fused));
+        if (!fused) RET(encode_dev_impl(*L.d, sv, k, m, st));
+    }
     std::vector<uint32_t> crc_tmp;
     if (meta_out) {
         CrcJob j;
@@ -1316,7 +1366,7 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
         crc_tmp.resize(n);
         CK(cudaMemcpyAsync(crc_tmp.data(), d_crc, 4 * static_cast<size_t>(n), cudaMemcpyDeviceToHost, st));
     }
-    for (int r = 0; r < m; r++) {
+    for (int r = 0; r < m && !parity_home; r++) {
         CK(cudaMemcpyAsync(shards_out[k + r], db + static_cast<size_t>(k + r) * pitch, S, cudaMemcpyDeviceToHost, st));
     }
     // systematic data shards are the padded input verbatim (erasure.rs:17-19): host copy while the GPU works
@@ -1328,6 +1378,7 @@ int gpu_ec_encode(const uint8_t *data, size_t len, int k, int m, uint8_t *const 
         if (have < S) memset(shards_out[j] + have, 0, S - have);
     }
     CK(cudaStreamSynchronize(st));
+    if (parity_home) CK(cudaStreamSynchronize(L.s->stream2));
     if (shard_crc_out) memcpy(shard_crc_out, crc_tmp.data(), 4 * static_cast<size_t>(n));
     if (full_crc_out) *full_crc_out = full_crc_host(crc_tmp.data(), S, len, GPU_EC_POLY_IEEE);
     return GPU_EC_OK;

@@ -10,6 +10,7 @@ signal.signal(signal.SIGPIPE, signal.SIG_DFL)  # `| head -1` must not raise Brok
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "rust-hadoop-generated-by-llm_b200"))
+sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 import gpu_ec
@@ -102,6 +103,36 @@ def fused63(n=64):
     print(f"rs(6,3) encode only: {ms:.3f} ms {a/ms/1e6:.0f} GB/s frac={a/ms/1e6/PEAK:.3f}")
 
 
+def bigcall():
+    """latency of ONE gpu_ec_encode call on a 256 MiB pinned block, RS(6,3), with shard CRCs (set GPU_EC_NO_CHUNKED_COPY=1 to compare)"""
+    import time
+    import zlib
+    from oracle import oracle
+    blk, k, m = 256 << 20, 6, 3
+    S = (blk + k - 1) // k
+    def pinned(nb):
+        p = C.c_void_p()
+        check(L.gpu_ec_alloc_pinned(C.byref(p), nb))
+        return p, np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nb,))
+    ps, src = pinned(blk)
+    pp, par = pinned(m * S)
+    src[:] = oracle.fill_synthetic(blk, 5)
+    ptrs = (C.c_void_p * (k + m))()
+    for r in range(m):
+        ptrs[k + r] = par.ctypes.data + r * S
+    crcs = np.zeros(k + m, np.uint32)
+    full = C.c_uint32(0)
+    ts = []
+    for _ in range(8):
+        t0 = time.perf_counter()
+        check(L.gpu_ec_encode(src.ctypes.data, blk, k, m, ptrs, crcs.ctypes.data, C.byref(full), None))
+        ts.append(time.perf_counter() - t0)
+    want = oracle.encode(src, k, m)
+    ok = np.array_equal(par.reshape(m, S), want[k:]) and crcs.tolist() == [zlib.crc32(x.tobytes()) for x in want] and full.value == zlib.crc32(src.tobytes())
+    print(f"gpu_ec_encode 256 MiB RS(6,3)+CRC, one caller: {min(ts[2:])*1e3:.2f} ms best, {sorted(ts[2:])[len(ts[2:])//2]*1e3:.2f} ms median, "
+          f"{blk/min(ts[2:])/1e9:.1f} data GB/s, chunked={'no' if os.environ.get('GPU_EC_NO_CHUNKED_COPY') else 'yes'}, parity_ok={ok}")
+
+
 def rs(k, m, stripe_len, n):
     S = gpu_ec.erasure.shard_len(stripe_len, k)
     b = device.StripeBatch(n, k, m, S)
@@ -129,6 +160,8 @@ if __name__ == "__main__":
         crc()
     elif what == "sfold":
         sfold()
+    elif what == "bigcall":
+        bigcall()
     elif what == "fused63":
         fused63(int(sys.argv[2]) if len(sys.argv) > 2 else 64)
     elif what == "fused":
