@@ -1401,6 +1401,32 @@ int gpu_ec_reconstruct(uint8_t *const *shards, const uint8_t *present, size_t sh
     RET(slot_reserve(*L.s, static_cast<size_t>(n) * pitch));
     cudaStream_t st = L.s->stream;
     uint8_t *db = L.s->dbuf;
+    static const bool no_chunks = getenv("GPU_EC_NO_CHUNKED_COPY") != nullptr;  // experiments only
+    if (L.alone && S * static_cast<size_t>(k) >= (64u << 20) && !no_chunks) {
+        // alone on the device: column chunks, rebuilt shards go home on a second stream while the next chunk comes in
+        // (same scheme as gpu_ec_encode)
+        RET(slot_overlap_init(*L.s));
+        cudaStream_t st2 = L.s->stream2;
+        const size_t width = round_up(div_up(S, 8), 4096);
+        int c = 0;
+        for (size_t c0 = 0; c0 < S; c0 += width, c++) {
+            const size_t w = std::min(width, S - c0);
+            for (int j = 0; j < k; j++) {
+                const int idx = plan.survivors[j];
+                CK(cudaMemcpyAsync(db + static_cast<size_t>(idx) * pitch + c0, shards[idx] + c0, w, cudaMemcpyHostToDevice, st));
+            }
+            gpu_ec_stripes blk{db + c0, pitch, static_cast<size_t>(n) * pitch, w, 1};
+            RET(launch_apply(*L.d, blk, plan.rows.data(), plan.survivors.data(), k, plan.missing.data(),
+                             static_cast<int>(plan.missing.size()), st));
+            CK(cudaEventRecord(L.s->ev[c], st));
+            CK(cudaStreamWaitEvent(st2, L.s->ev[c], 0));
+            for (int idx : plan.missing)
+                CK(cudaMemcpyAsync(shards[idx] + c0, db + static_cast<size_t>(idx) * pitch + c0, w, cudaMemcpyDeviceToHost, st2));
+        }
+        CK(cudaStreamSynchronize(st));
+        CK(cudaStreamSynchronize(st2));
+        return GPU_EC_OK;
+    }
     for (int j = 0; j < k; j++) {
         const int idx = plan.survivors[j];
         CK(cudaMemcpyAsync(db + static_cast<size_t>(idx) * pitch, shards[idx], S, cudaMemcpyHostToDevice, st));

@@ -183,6 +183,19 @@ def test_reference_roundtrip_fixtures(L):
     assert np.array_equal(erasure.decode(opt, 2, 2, blk.size), blk)
 
 
+def test_reconstruct_large_single_call_chunked(L, orc):
+    """A >= 64 MiB stripe through the host-pointer reconstruct: the call walks it in column chunks with the rebuilt
+    shards copied back on a second stream (chunkserver.rs:620-623 on a large block); bytes must not change."""
+    k, m = 6, 3
+    data = orc.fill_synthetic((66 << 20) + 13, 0xEC0000E1)
+    sh = orc.encode(data, k, m)
+    for missing in ([1, 4, 7], [0], [6, 8]):
+        opt = [None if i in missing else sh[i].copy() for i in range(k + m)]
+        erasure.reconstruct(opt, k, m)
+        for i in missing:
+            assert np.array_equal(opt[i], sh[i]), (missing, i)
+
+
 def test_reconstruct_config3_worst_case_stripe(L, orc):
     # one 1 MiB stripe at RS(6,3), 2 data + 1 parity lost: S = 174 763
     data = orc.fill_synthetic(1 << 20, 0xEC000003)
